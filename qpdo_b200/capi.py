@@ -173,7 +173,7 @@ class Result(object):
     __slots__ = ("x", "y", "prim_inf_cert", "dual_inf_cert", "status_val", "status",
                  "iterations", "oterations", "objective", "res_prim_norm", "res_dual_norm",
                  "res_prim_in_norm", "res_dual_in_norm", "setup_time", "solve_time", "run_time",
-                 "active_set")
+                 "active_set", "wall_setup", "wall_solve")
 
     def __repr__(self):
         return ("Result(status=%r(%d), iter=%d, oter=%d, obj=%.15g, rp=%.3e, rd=%.3e)" %
@@ -315,3 +315,50 @@ class Solver(object):
             self.delete()
         except Exception:
             pass
+
+
+# --------------------------------------------------------------------------- qpdo_cuda.h mirror
+class DevScalars(C.Structure):
+    _fields_ = [("res_prim_norm", C.c_double), ("res_dual_norm", C.c_double), ("res_prim_in_norm", C.c_double),
+                ("res_dual_in_norm", C.c_double), ("tau", C.c_double), ("ls_eta", C.c_double), ("ls_beta", C.c_double),
+                ("objective", C.c_double), ("inf_a", C.c_double), ("inf_b", C.c_double), ("inf_c", C.c_double),
+                ("sigma", C.c_double), ("n_active", C.c_int), ("n_enter", C.c_int), ("n_leave", C.c_int),
+                ("n_mu_changed", C.c_int), ("reset_newton", C.c_int), ("factor_mode", C.c_int), ("ls_nL", C.c_int),
+                ("not_posdef", C.c_int), ("flag", C.c_int), ("n_refactor", C.c_int), ("n_update", C.c_int),
+                ("n_qonly", C.c_int), ("pad", C.c_int)]
+
+
+class DevProfile(C.Structure):
+    _fields_ = [("assemble_ms", C.c_double), ("factor_ms", C.c_double), ("solve_ms", C.c_double),
+                ("spmv_ms", C.c_double), ("linesearch_ms", C.c_double), ("residual_ms", C.c_double),
+                ("other_ms", C.c_double), ("n_newton", C.c_long), ("n_residual", C.c_long),
+                ("kernel_launches", C.c_long)]
+
+
+class DevSymbolicInfo(C.Structure):
+    _fields_ = [("nsuper", C.c_int), ("nlevel", C.c_int), ("max_front", C.c_int), ("max_nc", C.c_int),
+                ("lnz", C.c_int64), ("lnz_stored", C.c_int64), ("usize", C.c_int64), ("nnzK", C.c_int64),
+                ("ntriple", C.c_int64), ("flops", C.c_double), ("analyze_seconds", C.c_double)]
+
+
+def declare_device_layer(lib):
+    """prototypes of the diagnostics / test entry points of include/qpdo_cuda.h"""
+    vp = C.c_void_p
+    lib.qpdo_dev_last_error.restype = C.c_char_p
+    lib.qpdo_dev_count.restype = C.c_int
+    lib.qpdo_dev_set_profiling.argtypes = [vp, C.c_int]
+    lib.qpdo_dev_get_profile.argtypes = [vp, C.POINTER(DevProfile), C.c_int]
+    lib.qpdo_dev_get_symbolic_info.argtypes = [vp, C.POINTER(DevSymbolicInfo)]
+    lib.qpdo_dev_get_vector.argtypes = [vp, C.c_char_p, _pd, C.c_long]
+    lib.qpdo_dev_get_vector.restype = C.c_long
+    lib.qpdo_dev_test_factor_solve.argtypes = [vp, _pd, C.c_double, _pd, _pd, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.qpdo_dev_test_spmv.argtypes = [vp, C.c_int, _pd, _pd]
+    return lib
+
+
+def dev_vector(lib, dev, name, cap):
+    out = np.zeros(max(1, cap))
+    n = lib.qpdo_dev_get_vector(dev, name.encode(), out.ctypes.data_as(_pd), cap)
+    if n < 0:
+        raise RuntimeError(lib.qpdo_dev_last_error().decode())
+    return out[:min(n, cap)]

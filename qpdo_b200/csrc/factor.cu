@@ -1,0 +1,553 @@
+// factor.cu -- numeric multifrontal Cholesky of K = Q + sigma I + A' diag(omega) A on the GPU, and
+// the supernodal triangular solves.  Replaces, for the Newton hot path, cholmod_aat + cholmod_add
+// (K assembly, cholmod_interface.c:45-48), cholmod_factorize_p / super_numeric (numeric
+// factorization, cholmod_interface.c:8-30; t_cholmod_super_numeric.c: dsyrk 682, dgemm 708,
+// dpotrf 864, dtrsm 997), cholmod_updown (cholmod_interface.c:57-93; here: numeric refactorization
+// with changed row weights on the fixed superset pattern) and cholmod_solve (cholmod_interface.c:98-102).
+//
+// Layout in HBM: one L panel per supernode (N x nc, column major, ld = N = nc + nr) in Lx, one
+// update matrix per supernode (nr x nr, lower, ld = nr) in Ux; all fronts resident at once.
+// Schedule: levels of the supernodal assembly tree, one launch per (level, size bucket); fronts
+// that fit in shared memory are factored by one CTA each, larger ones by a blocked right-looking
+// panel loop (potrf 32x32 -> trsm -> rank-32 SYRK on the FP64 tensor pipe, mma.sync m8n8k4 DMMA).
+// The whole sequence is captured once into a CUDA graph and replayed every Newton step.
+#include "dev_internal.h"
+#include <algorithm>
+
+#define NB 32          // panel width of the blocked path
+#define CW 32          // destination-column chunk of the big-front assembly
+#define TS 64          // SYRK tile
+#define PLD 36         // padded leading dimension of a 64 x 32 panel tile in smem (conflict free)
+
+struct FArgs {
+    const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
+    const int64_t *sn_rowptr, *Lp, *Up;
+    double *Lx, *Ux;
+    qpdo_dev_scalars *sc;
+};
+
+// ------------------------------------------------------------------------------- K assembly
+// Lx[Kdst[e]] = Q_e + sum_t omega[row_t] * (a_ir a_ic)_t (+ sigma on the diagonal): the fused
+// replacement of cholmod_aat + cholmod_add + the beta*I of cholmod_factorize_p; Lx was zeroed.
+__global__ void k_assemble_K(int64_t nnzK, const int64_t *Kdst, const int *Kq, const int64_t *Ktp, const int *Kt_row,
+                             const double *Kt_val, const int *Ki, const int *Kcol, const double *Qx, const double *omega,
+                             const qpdo_dev_scalars *sc, double *Lx)
+{
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nnzK) return;
+    double v = 0.0;
+    for (int64_t t = Ktp[e]; t < Ktp[e + 1]; t++) v = fma(omega[Kt_row[t]], Kt_val[t], v);
+    int q = Kq[e];
+    if (q >= 0) v += Qx[q];
+    if (Ki[e] == Kcol[e]) v += sc->sigma;
+    Lx[Kdst[e]] = v;
+}
+__global__ void k_products(int64_t nt, const int *a1, const int *a2, const double *Ax, double *val)
+{
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < nt) val[t] = Ax[a1[t]] * Ax[a2[t]];
+}
+
+// ------------------------------------------------------------------------------- smem fronts
+// One CTA per front: load the panel, extend-add the children's update matrices in fixed order,
+// eliminate the nc pivot columns (right-looking), write the panel and the Schur complement.
+template <int NT>
+__global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
+{
+    extern __shared__ double F[];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr, ld = N | 1;
+    double *Lp = A.Lx + A.Lp[s];
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; F[i + j * ld] = Lp[idx]; }
+    for (int idx = tid; idx < N * nr; idx += NT) { int j = idx / N, i = idx - j * N; F[i + (nc + j) * ld] = 0.0; }
+    __syncthreads();
+    for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
+        const int c = A.child_idx[t], rc = A.sn_nr[c];
+        const int *rl = A.rel + A.sn_rowptr[c];
+        const double *U = A.Ux + A.Up[c];
+        for (int idx = tid; idx < rc * rc; idx += NT) {
+            int j = idx / rc, i = idx - j * rc;
+            if (i >= j) F[rl[i] + rl[j] * ld] += U[idx];
+        }
+        __syncthreads();
+    }
+    const int lane = tid & 31, wid = tid >> 5, NW = NT / 32;
+    for (int k = 0; k < nc; k++) {
+        const double piv = F[k + k * ld];
+        const double dk = sqrt(piv);
+        __syncthreads();
+        if (tid == 0 && !(piv > 0.0)) A.sc->not_posdef = 1;
+        for (int i = k + tid; i < N; i += NT) F[i + k * ld] = (i == k) ? dk : F[i + k * ld] / dk;
+        __syncthreads();
+        for (int j = k + 1 + wid; j < N; j += NW) {
+            const double ljk = F[j + k * ld];
+            for (int i = j + lane; i < N; i += 32) F[i + j * ld] = fma(-F[i + k * ld], ljk, F[i + j * ld]);
+        }
+        __syncthreads();
+    }
+    for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; Lp[idx] = (i >= j) ? F[i + j * ld] : 0.0; }
+    double *U = A.Ux + A.Up[s];
+    for (int idx = tid; idx < nr * nr; idx += NT) {
+        int j = idx / nr, i = idx - j * nr;
+        if (i >= j) U[idx] = F[(nc + i) + (nc + j) * ld];
+    }
+}
+
+// ------------------------------------------------------------------------------- big fronts
+__device__ __forceinline__ double *front_elem(const FArgs &A, int s, int nc, int nr, int N, int i, int j)
+{   // element (i, j), i >= j, of the front: L panel for j < nc, update matrix otherwise
+    return (j < nc) ? (A.Lx + A.Lp[s] + (int64_t)j * N + i) : (A.Ux + A.Up[s] + (int64_t)(j - nc) * nr + (i - nc));
+}
+// CTA (front, chunk) owns destination columns [c0, c1): zero their update-matrix part, then add the
+// children's contributions that fall into these columns, children in fixed order.
+__global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
+{
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    const int c0 = blockIdx.y * CW;
+    if (c0 >= N) return;
+    const int c1 = min(N, c0 + CW), tid = threadIdx.x;
+    for (int j = max(c0, nc); j < c1; j++) {
+        double *col = A.Ux + A.Up[s] + (int64_t)(j - nc) * nr;
+        for (int i = j - nc + tid; i < nr; i += 256) col[i] = 0.0;
+    }
+    __syncthreads();
+    for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
+        const int c = A.child_idx[t], rc = A.sn_nr[c];
+        const int *rl = A.rel + A.sn_rowptr[c];
+        const double *U = A.Ux + A.Up[c];
+        int lo = 0, hi = rc;                       // first jj with rl[jj] >= c0
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (rl[mid] < c0) lo = mid + 1; else hi = mid; }
+        for (int jj = lo; jj < rc; jj++) {
+            const int dc = rl[jj];
+            if (dc >= c1) break;
+            const double *ucol = U + (int64_t)jj * rc;
+            for (int ii = jj + tid; ii < rc; ii += 256) {
+                double *dst = front_elem(A, s, nc, nr, N, rl[ii], dc);
+                *dst += ucol[ii];
+            }
+        }
+        __syncthreads();
+    }
+}
+// factor the nb x nb diagonal block at (kb, kb)
+__global__ void __launch_bounds__(256) k_big_potrf(FArgs A, const int *list, int kb)
+{
+    __shared__ double D[NB][NB + 1];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    if (kb >= nc) return;
+    const int nb = min(NB, nc - kb), tid = threadIdx.x;
+    double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N + kb;
+    for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; D[i][j] = Lb[(int64_t)j * N + i]; }
+    __syncthreads();
+    const int lane = tid & 31, wid = tid >> 5;
+    for (int k = 0; k < nb; k++) {
+        const double piv = D[k][k], dk = sqrt(piv);
+        __syncthreads();
+        if (tid == 0 && !(piv > 0.0)) A.sc->not_posdef = 1;
+        if (tid >= k && tid < nb) D[tid][k] = (tid == k) ? dk : D[tid][k] / dk;
+        __syncthreads();
+        for (int j = k + 1 + wid; j < nb; j += 8) {
+            const double ljk = D[j][k];
+            if (lane >= j && lane < nb) D[lane][j] = fma(-D[lane][k], ljk, D[lane][j]);
+        }
+        __syncthreads();
+    }
+    for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; Lb[(int64_t)j * N + i] = (i >= j) ? D[i][j] : 0.0; }
+}
+// rows below the diagonal block: X <- X L11^{-T}, one row per thread
+__global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int kb)
+{
+    __shared__ double D[NB][NB + 1];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    if (kb >= nc) return;
+    const int nb = min(NB, nc - kb), tid = threadIdx.x;
+    const int r0 = kb + nb + blockIdx.y * 128;
+    if (r0 >= N) return;
+    double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N;
+    for (int idx = tid; idx < NB * NB; idx += 128) {
+        int j = idx / NB, i = idx - j * NB;
+        D[i][j] = (i < nb && j < nb) ? Lb[(int64_t)j * N + kb + i] : (i == j ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    const int i = r0 + tid;
+    if (i >= N) return;
+    double x[NB];
+#pragma unroll
+    for (int j = 0; j < NB; j++) x[j] = (j < nb) ? Lb[(int64_t)j * N + i] : 0.0;
+#pragma unroll
+    for (int j = 0; j < NB; j++) {
+        double v = x[j];
+#pragma unroll
+        for (int k = 0; k < j; k++) v = fma(-x[k], D[j][k], v);
+        x[j] = v / D[j][j];
+    }
+#pragma unroll
+    for (int j = 0; j < NB; j++) if (j < nb) Lb[(int64_t)j * N + i] = x[j];
+}
+// trailing update C -= P P' for the lower 64 x 64 tiles, P = panel rows x nb; FP64 tensor pipe
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int kb)
+{
+    __shared__ double Pa[TS * PLD], Pb[TS * PLD];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    if (kb >= nc) return;
+    const int nb = min(NB, nc - kb);
+    const int r0 = kb + nb, R = N - r0;
+    if (R <= 0) return;
+    const int nt = (R + TS - 1) / TS;
+    int ti = (int)((sqrt(8.0 * blockIdx.y + 1.0) - 1.0) * 0.5);
+    while ((ti + 1) * (ti + 2) / 2 <= (int)blockIdx.y) ti++;
+    while (ti * (ti + 1) / 2 > (int)blockIdx.y) ti--;
+    const int tj = blockIdx.y - ti * (ti + 1) / 2;
+    if (ti >= nt) return;
+    const int tid = threadIdx.x;
+    const double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N;
+    const int ra = r0 + ti * TS, rb = r0 + tj * TS;
+    for (int idx = tid; idx < TS * NB; idx += 256) {
+        int k = idx / TS, r = idx - k * TS;                 // consecutive threads -> consecutive rows
+        Pa[r * PLD + k] = (k < nb && ra + r < N) ? Lb[(int64_t)k * N + ra + r] : 0.0;
+        Pb[r * PLD + k] = (k < nb && rb + r < N) ? Lb[(int64_t)k * N + rb + r] : 0.0;
+    }
+    __syncthreads();
+    const int lane = tid & 31, wid = tid >> 5;
+    const int wr = (wid & 1) * 32, wc = (wid >> 1) * 16;    // warp tile: 32 rows x 16 cols
+    const int g = lane >> 2, q = lane & 3;
+    double acc[4][2][2];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ks++) {
+        double af[4], bf[2];
+#pragma unroll
+        for (int a = 0; a < 4; a++) af[a] = Pa[(wr + a * 8 + g) * PLD + ks * 4 + q];
+#pragma unroll
+        for (int b = 0; b < 2; b++) bf[b] = Pb[(wc + b * 8 + g) * PLD + ks * 4 + q];
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+            for (int b = 0; b < 2; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int gi = ra + wr + a * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
+                if (gi < N && gj <= gi) { double *dst = front_elem(A, s, nc, nr, N, gi, gj); *dst -= acc[a][b][e]; }
+            }
+}
+
+// ------------------------------------------------------------------------------- triangular solves
+struct SArgs {
+    const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
+    const int64_t *sn_rowptr, *Lp;
+    const double *Lx;
+    double *xs, *uv;
+};
+// forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t; u_s = children's pass-through - L21 y_s
+template <int NT>
+__global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
+{
+    extern __shared__ double vec[];                    // N entries + NB for the block solution
+    __shared__ double D[NB][NB + 1];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    const double *L = A.Lx + A.Lp[s];
+    const int tid = threadIdx.x, lane = tid & 31;
+    double *yb = vec + N;
+    for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : 0.0;
+    __syncthreads();
+    for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
+        const int c = A.child_idx[t], rc = A.sn_nr[c];
+        const int *rl = A.rel + A.sn_rowptr[c];
+        const double *u = A.uv + A.sn_rowptr[c];
+        for (int i = tid; i < rc; i += NT) vec[rl[i]] += u[i];
+        __syncthreads();
+    }
+    for (int kb = 0; kb < nc; kb += NB) {
+        const int nb = min(NB, nc - kb);
+        for (int idx = tid; idx < nb * nb; idx += NT) { int j = idx / nb, i = idx - j * nb; D[i][j] = L[(int64_t)(kb + j) * N + kb + i]; }
+        __syncthreads();
+        if (tid < 32) {
+            double v = (lane < nb) ? vec[kb + lane] : 0.0;
+            for (int k = 0; k < nb; k++) {
+                if (lane == k) v = v / D[k][k];
+                const double yk = __shfl_sync(0xffffffffu, v, k);
+                if (lane > k && lane < nb) v = fma(-D[lane][k], yk, v);
+            }
+            if (lane < nb) { yb[lane] = v; A.xs[f + kb + lane] = v; }
+        }
+        __syncthreads();
+        for (int i = kb + nb + tid; i < N; i += NT) {
+            const double *Li = L + (int64_t)kb * N + i;
+            double acc = 0.0;
+#pragma unroll 8
+            for (int k = 0; k < nb; k++) acc = fma(Li[(int64_t)k * N], yb[k], acc);
+            vec[i] -= acc;
+        }
+        __syncthreads();
+    }
+    double *u = A.uv + A.sn_rowptr[s];
+    for (int i = tid; i < nr; i += NT) u[i] = vec[nc + i];
+}
+// backward: x_s = L11^{-T} (y_s - L21' x_rows)
+template <int NT>
+__global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
+{
+    extern __shared__ double vec[];
+    __shared__ double D[NB][NB + 1];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    const double *L = A.Lx + A.Lp[s];
+    const int *rows = A.rows + A.sn_rowptr[s];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NW = NT / 32;
+    for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : A.xs[rows[i - nc]];
+    __syncthreads();
+    const int nblk = (nc + NB - 1) / NB;
+    for (int b = nblk - 1; b >= 0; b--) {
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        for (int idx = tid; idx < nb * nb; idx += NT) { int j = idx / nb, i = idx - j * nb; D[i][j] = L[(int64_t)(kb + j) * N + kb + i]; }
+        // t_k = vec[k] - sum_{i >= kb+nb} L[i,k] vec[i], one warp per column
+        for (int k = wid; k < nb; k += NW) {
+            const double *Lk = L + (int64_t)(kb + k) * N;
+            double acc = 0.0;
+            for (int i = kb + nb + lane; i < N; i += 32) acc = fma(Lk[i], vec[i], acc);
+            for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) vec[kb + k] -= acc;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            double v = (lane < nb) ? vec[kb + lane] : 0.0;
+            for (int k = nb - 1; k >= 0; k--) {
+                if (lane == k) v = v / D[k][k];
+                const double xk = __shfl_sync(0xffffffffu, v, k);
+                if (lane < k) v = fma(-D[k][lane], xk, v);
+            }
+            if (lane < nb) { vec[kb + lane] = v; A.xs[f + kb + lane] = v; }
+        }
+        __syncthreads();
+    }
+}
+__global__ void k_permute_in(const double *rhs, const int *perm, double *xs, int n)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) xs[k] = rhs[perm[k]];
+}
+__global__ void k_permute_out(const double *xs, const int *perm, double *x, int n)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) x[perm[k]] = xs[k];
+}
+
+// =============================================================================== host side
+static const int BUCKET_N[4] = {32, 64, 104, 150};       // smem-front size classes (front order N)
+static const int SOLVE_WARP_N = 64;                       // fronts up to this order are solved by one warp
+
+static FArgs fargs(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    FArgs A;
+    A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Up = F.Up; A.Lx = F.Lx; A.Ux = F.Ux; A.sc = d->sc;
+    return A;
+}
+static SArgs sargs(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    SArgs A;
+    A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.xs = F.xs; A.uv = F.uv;
+    return A;
+}
+
+int factor_setup(qpdo_dev *d, int ordering)
+{
+    Factor &F = d->F;
+    const int n = d->n, m = d->m;
+    // pull the patterns back from the problem that dev_core uploaded: simpler to re-read host copies
+    std::vector<int> Qp(n + 1), Qi(d->nnzQ ? d->nnzQ : 1), Ap(n + 1), Ai(d->nnzA ? d->nnzA : 1);
+    CUDA_OK(cudaMemcpyAsync(Qp.data(), d->Qp, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaMemcpyAsync(Ap.data(), d->Ap, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
+    if (d->nnzQ) CUDA_OK(cudaMemcpyAsync(Qi.data(), d->Qi, sizeof(int) * d->nnzQ, cudaMemcpyDeviceToHost, d->st));
+    if (d->nnzA) CUDA_OK(cudaMemcpyAsync(Ai.data(), d->Ai, sizeof(int) * d->nnzA, cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaStreamSynchronize(d->st));
+    char err[256];
+    qpdo_symbolic *S = qpdo_symbolic_analyze(n, m, Qp.data(), Qi.data(), Ap.data(), Ai.data(), ordering, err);
+    if (!S) { qpdo_set_error("symbolic analysis failed: %s", err); return -1; }
+    F.S = S;
+    const int ns = S->nsuper;
+    const int64_t nrows = S->sn_rowptr[ns];
+    std::vector<int> Kcol(S->nnzK);
+    for (int k = 0; k < n; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++) Kcol[e] = k;
+    if (dev_upload(d, &F.sn_start, S->sn_start, ns + 1) || dev_upload(d, &F.sn_nr, S->sn_nr, ns) ||
+        dev_upload(d, &F.rows, S->rows, nrows) || dev_upload(d, &F.rel, S->rel, nrows) ||
+        dev_upload(d, &F.child_ptr, S->child_ptr, ns + 1) || dev_upload(d, &F.child_idx, S->child_idx, ns) ||
+        dev_upload(d, &F.level_sn, S->level_sn, ns) || dev_upload(d, &F.sn_rowptr, S->sn_rowptr, ns + 1) ||
+        dev_upload(d, &F.Lp, S->Lp, ns + 1) || dev_upload(d, &F.Up, S->Up, ns + 1) ||
+        dev_upload(d, &F.perm, S->perm, n) || dev_upload(d, &F.pinv, S->pinv, n) ||
+        dev_upload(d, &F.Ki, S->Ki, S->nnzK) || dev_upload(d, &F.Kcol, Kcol.data(), S->nnzK) ||
+        dev_upload(d, &F.Kq, S->Kq, S->nnzK) || dev_upload(d, &F.Kdst, S->Kdst, S->nnzK) ||
+        dev_upload(d, &F.Ktp, S->Ktp, S->nnzK + 1) || dev_upload(d, &F.Kt_row, S->Kt_row, S->ntriple) ||
+        dev_upload(d, &F.Kt_a1, S->Kt_a1, S->ntriple) || dev_upload(d, &F.Kt_a2, S->Kt_a2, S->ntriple) ||
+        dev_alloc(d, &F.Kt_val, S->ntriple) || dev_alloc(d, &F.Lx, S->lnz_stored) || dev_alloc(d, &F.Ux, S->usize) ||
+        dev_alloc(d, &F.xs, n) || dev_alloc(d, &F.uv, nrows))
+        return -1;
+    // launch plan: per level, fronts are sorted by decreasing order N
+    F.plan.assign(S->nlevel, std::vector<FrontLaunch>());
+    for (int lv = 0; lv < S->nlevel; lv++) {
+        int b = S->level_ptr[lv], e = S->level_ptr[lv + 1];
+        auto ordN = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s] + S->sn_nr[s]; };
+        auto ncOf = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s]; };
+        int pos = b;
+        // big fronts first
+        int q = pos;
+        while (q < e && ordN(q) > BUCKET_N[3]) q++;
+        if (q > pos) {
+            FrontLaunch L; L.first = pos; L.count = q - pos; L.kind = 2; L.maxN = ordN(pos); L.maxnc = 0;
+            for (int t = pos; t < q; t++) L.maxnc = std::max(L.maxnc, ncOf(t));
+            F.plan[lv].push_back(L); pos = q;
+        }
+        for (int bk = 3; bk >= 0 && pos < e; bk--) {
+            int lo = bk > 0 ? BUCKET_N[bk - 1] : 0;
+            q = pos;
+            while (q < e && ordN(q) > lo) q++;
+            if (q > pos) {
+                FrontLaunch L; L.first = pos; L.count = q - pos; L.kind = (bk == 0) ? 0 : 1; L.maxN = ordN(pos); L.maxnc = bk;
+                F.plan[lv].push_back(L); pos = q;
+            }
+        }
+    }
+    cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    return 0;
+}
+
+int factor_refresh_products(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    if (F.S->ntriple) k_products<<<cdiv(F.S->ntriple, 256), 256, 0, d->st>>>(F.S->ntriple, F.Kt_a1, F.Kt_a2, d->Ax, F.Kt_val);
+    return 0;
+}
+
+static long issue_factor(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    const qpdo_symbolic *S = F.S;
+    FArgs A = fargs(d);
+    long launches = 0;
+    for (int lv = 0; lv < S->nlevel; lv++)
+        for (const FrontLaunch &L : F.plan[lv]) {
+            const int *list = F.level_sn + L.first;
+            if (L.kind == 2) {
+                k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, d->st>>>(A, list); launches++;
+                for (int kb = 0; kb < L.maxnc; kb += NB) {
+                    k_big_potrf<<<L.count, 256, 0, d->st>>>(A, list, kb); launches++;
+                    int R = L.maxN - kb - 1;
+                    if (R > 0) {
+                        k_big_trsm<<<dim3(L.count, cdiv(R, 128)), 128, 0, d->st>>>(A, list, kb);
+                        int nt = cdiv(R, TS);
+                        k_big_syrk<<<dim3(L.count, nt * (nt + 1) / 2), 256, 0, d->st>>>(A, list, kb);
+                        launches += 2;
+                    }
+                }
+            } else {
+                size_t smem = sizeof(double) * (size_t)(L.maxN | 1) * L.maxN;
+                if (L.maxnc == 0) k_front_smem<64><<<L.count, 64, smem, d->st>>>(A, list);
+                else if (L.maxnc == 1) k_front_smem<128><<<L.count, 128, smem, d->st>>>(A, list);
+                else k_front_smem<256><<<L.count, 256, smem, d->st>>>(A, list);
+                launches++;
+            }
+        }
+    return launches;
+}
+static long issue_solve(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    const qpdo_symbolic *S = F.S;
+    SArgs A = sargs(d);
+    long launches = 0;
+    auto ordN = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s] + S->sn_nr[s]; };
+    for (int pass = 0; pass < 2; pass++)
+        for (int t = 0; t < S->nlevel; t++) {
+            int lv = pass == 0 ? t : S->nlevel - 1 - t;
+            int b = S->level_ptr[lv], e = S->level_ptr[lv + 1], q = b;
+            while (q < e && ordN(q) > SOLVE_WARP_N) q++;
+            if (q > b) {
+                size_t smem = sizeof(double) * (ordN(b) + NB);
+                if (pass == 0) k_fwd<256><<<q - b, 256, smem, d->st>>>(A, F.level_sn + b);
+                else k_bwd<256><<<q - b, 256, smem, d->st>>>(A, F.level_sn + b);
+                launches++;
+            }
+            if (e > q) {
+                size_t smem = sizeof(double) * (ordN(q) + NB);
+                if (pass == 0) k_fwd<32><<<e - q, 32, smem, d->st>>>(A, F.level_sn + q);
+                else k_bwd<32><<<e - q, 32, smem, d->st>>>(A, F.level_sn + q);
+                launches++;
+            }
+        }
+    return launches;
+}
+static int capture(qpdo_dev *d, long (*issue)(qpdo_dev *), cudaGraphExec_t *out, long *launches)
+{
+    cudaGraph_t g = nullptr;
+    CUDA_OK(cudaStreamBeginCapture(d->st, cudaStreamCaptureModeThreadLocal));
+    *launches = issue(d);
+    CUDA_OK(cudaStreamEndCapture(d->st, &g));
+    CUDA_OK(cudaGraphInstantiate(out, g, 0));
+    cudaGraphDestroy(g);
+    return 0;
+}
+
+int factor_numeric(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    const qpdo_symbolic *S = F.S;
+    {
+        PhaseTimer t(d, PH_ASSEMBLE);
+        CUDA_OK(cudaMemsetAsync(F.Lx, 0, sizeof(double) * S->lnz_stored, d->st));
+        k_assemble_K<<<cdiv(S->nnzK, 256), 256, 0, d->st>>>(S->nnzK, F.Kdst, F.Kq, F.Ktp, F.Kt_row, F.Kt_val, F.Ki, F.Kcol,
+                                                            d->Qx, d->omega, d->sc, F.Lx);
+        d->prof.kernel_launches += 2;
+    }
+    {
+        PhaseTimer t(d, PH_FACTOR);
+        if (!F.g_factor && capture(d, issue_factor, &F.g_factor, &F.launches_factor)) return -1;
+        CUDA_OK(cudaGraphLaunch(F.g_factor, d->st));
+        d->prof.kernel_launches += F.launches_factor;
+    }
+    return 0;
+}
+
+int factor_solve(qpdo_dev *d, const double *rhs, double *x)
+{
+    Factor &F = d->F;
+    PhaseTimer t(d, PH_SOLVE);
+    k_permute_in<<<cdiv(d->n, 256), 256, 0, d->st>>>(rhs, F.perm, F.xs, d->n);
+    if (!F.g_solve && capture(d, issue_solve, &F.g_solve, &F.launches_solve)) return -1;
+    CUDA_OK(cudaGraphLaunch(F.g_solve, d->st));
+    k_permute_out<<<cdiv(d->n, 256), 256, 0, d->st>>>(F.xs, F.perm, x, d->n);
+    d->prof.kernel_launches += F.launches_solve + 2;
+    return 0;
+}
+
+void factor_destroy(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    if (F.g_factor) cudaGraphExecDestroy(F.g_factor);
+    if (F.g_solve) cudaGraphExecDestroy(F.g_solve);
+    F.g_factor = F.g_solve = nullptr;
+    if (F.S) qpdo_symbolic_free(F.S);
+    F.S = nullptr;
+}
