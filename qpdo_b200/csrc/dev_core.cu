@@ -301,7 +301,7 @@ extern "C" int qpdo_dev_create(qpdo_dev **out, const qpdo_dev_problem *p, int sc
         for (auto pp : mv) if (dev_alloc(d, pp, m)) bad = true;
         if (bad) break;
         if (dev_upload(d, &d->q, p->q, n) || dev_upload(d, &d->l, p->l, m) || dev_upload(d, &d->u, p->u, m)) break;
-        if (dev_alloc(d, &d->act, m) || dev_alloc(d, &d->act_old, m) || dev_alloc(d, &d->sc, 1) || dev_alloc(d, &d->red, 64)) break;
+        if (dev_alloc(d, &d->act, m) || dev_alloc(d, &d->act_old, m) || dev_alloc(d, &d->sc, 1) || dev_alloc(d, &d->red, 1024)) break;
         if (cudaMallocHost((void **)&d->sc_host, sizeof(qpdo_dev_scalars)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); break; }
         memset(d->sc_host, 0, sizeof(qpdo_dev_scalars));
         // symbolic analysis on the host (pattern only, independent of the scaling)
