@@ -1,4 +1,4 @@
-// factor.cu -- numeric multifrontal Cholesky of K = Q + sigma I + A' diag(omega) A on the GPU, and
+// factor.cu -- numeric multifrontal LDL' factorization of K = Q + sigma I + A' diag(omega) A on the GPU, and
 // the supernodal triangular solves.  Replaces, for the Newton hot path, cholmod_aat + cholmod_add
 // (K assembly, cholmod_interface.c:45-48), cholmod_factorize_p / super_numeric (numeric
 // factorization, cholmod_interface.c:8-30; t_cholmod_super_numeric.c: dsyrk 682, dgemm 708,
@@ -9,7 +9,7 @@
 // update matrix per supernode (nr x nr, lower, ld = nr) in Ux; all fronts resident at once.
 // Schedule: levels of the supernodal assembly tree, one launch per (level, size bucket); fronts
 // that fit in shared memory are factored by one CTA each, larger ones by a blocked right-looking
-// panel loop (potrf 32x32 -> trsm -> rank-32 SYRK on the FP64 tensor pipe, mma.sync m8n8k4 DMMA).
+// panel loop (LDL' 32x32 -> trsm -> rank-32 SYRK on the FP64 tensor pipe, mma.sync m8n8k4 DMMA).
 // The whole sequence is captured once into a CUDA graph and replayed every Newton step.
 #include "dev_internal.h"
 #include <algorithm>
@@ -73,19 +73,18 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
         __syncthreads();
     }
     const int lane = tid & 31, wid = tid >> 5, NW = NT / 32;
+    // right-looking LDL': column k stays unscaled (= L D) while it updates the trailing matrix
     for (int k = 0; k < nc; k++) {
-        const double piv = F[k + k * ld];
-        const double dk = sqrt(piv);
-        __syncthreads();
-        if (tid == 0 && !(piv > 0.0)) A.sc->not_posdef = 1;
-        for (int i = k + tid; i < N; i += NT) F[i + k * ld] = (i == k) ? dk : F[i + k * ld] / dk;
-        __syncthreads();
+        const double dk = F[k + k * ld];
+        if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
         for (int j = k + 1 + wid; j < N; j += NW) {
-            const double ljk = F[j + k * ld];
+            const double ljk = F[j + k * ld] / dk;
             for (int i = j + lane; i < N; i += 32) F[i + j * ld] = fma(-F[i + k * ld], ljk, F[i + j * ld]);
         }
         __syncthreads();
+        for (int i = k + 1 + tid; i < N; i += NT) F[i + k * ld] = F[i + k * ld] / dk;
     }
+    __syncthreads();
     for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; Lp[idx] = (i >= j) ? F[i + j * ld] : 0.0; }
     double *U = A.Ux + A.Up[s];
     for (int idx = tid; idx < nr * nr; idx += NT) {
@@ -131,7 +130,7 @@ __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
         __syncthreads();
     }
 }
-// factor the nb x nb diagonal block at (kb, kb)
+// LDL' of the nb x nb diagonal block at (kb, kb): unit lower L11, D on the diagonal
 __global__ void __launch_bounds__(256) k_big_potrf(FArgs A, const int *list, int kb)
 {
     __shared__ double D[NB][NB + 1];
@@ -144,20 +143,19 @@ __global__ void __launch_bounds__(256) k_big_potrf(FArgs A, const int *list, int
     __syncthreads();
     const int lane = tid & 31, wid = tid >> 5;
     for (int k = 0; k < nb; k++) {
-        const double piv = D[k][k], dk = sqrt(piv);
-        __syncthreads();
-        if (tid == 0 && !(piv > 0.0)) A.sc->not_posdef = 1;
-        if (tid >= k && tid < nb) D[tid][k] = (tid == k) ? dk : D[tid][k] / dk;
-        __syncthreads();
+        const double dk = D[k][k];
+        if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
         for (int j = k + 1 + wid; j < nb; j += 8) {
-            const double ljk = D[j][k];
+            const double ljk = D[j][k] / dk;
             if (lane >= j && lane < nb) D[lane][j] = fma(-D[lane][k], ljk, D[lane][j]);
         }
         __syncthreads();
+        if (tid > k && tid < nb) D[tid][k] = D[tid][k] / dk;
     }
+    __syncthreads();
     for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; Lb[(int64_t)j * N + i] = (i >= j) ? D[i][j] : 0.0; }
 }
-// rows below the diagonal block: X <- X L11^{-T}, one row per thread
+// rows below the diagonal block: X <- X L11^{-T} D^{-1}, one row per thread
 __global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int kb)
 {
     __shared__ double D[NB][NB + 1];
@@ -178,17 +176,20 @@ __global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int 
     double x[NB];
 #pragma unroll
     for (int j = 0; j < NB; j++) x[j] = (j < nb) ? Lb[(int64_t)j * N + i] : 0.0;
+    // W = B L11^{-T} (unit lower L11), then X = W D^{-1}
 #pragma unroll
     for (int j = 0; j < NB; j++) {
         double v = x[j];
 #pragma unroll
         for (int k = 0; k < j; k++) v = fma(-x[k], D[j][k], v);
-        x[j] = v / D[j][j];
+        x[j] = v;
     }
+#pragma unroll
+    for (int j = 0; j < NB; j++) x[j] = x[j] / D[j][j];
 #pragma unroll
     for (int j = 0; j < NB; j++) if (j < nb) Lb[(int64_t)j * N + i] = x[j];
 }
-// trailing update C -= P P' for the lower 64 x 64 tiles, P = panel rows x nb; FP64 tensor pipe
+// trailing update C -= (X D) X' for the lower 64 x 64 tiles, X = panel rows x nb; FP64 tensor pipe
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b)
 {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
@@ -214,7 +215,7 @@ __global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int 
     const int ra = r0 + ti * TS, rb = r0 + tj * TS;
     for (int idx = tid; idx < TS * NB; idx += 256) {
         int k = idx / TS, r = idx - k * TS;                 // consecutive threads -> consecutive rows
-        Pa[r * PLD + k] = (k < nb && ra + r < N) ? Lb[(int64_t)k * N + ra + r] : 0.0;
+        Pa[r * PLD + k] = (k < nb && ra + r < N) ? Lb[(int64_t)k * N + ra + r] * Lb[(int64_t)k * N + kb + k] : 0.0;
         Pb[r * PLD + k] = (k < nb && rb + r < N) ? Lb[(int64_t)k * N + rb + r] : 0.0;
     }
     __syncthreads();
@@ -256,7 +257,8 @@ struct SArgs {
     const double *Lx;
     double *xs, *uv;
 };
-// forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t; u_s = children's pass-through - L21 y_s
+// forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t (unit lower); z_s = D^{-1} y_s is stored;
+// u_s = children's pass-through - L21 y_s
 template <int NT>
 __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
 {
@@ -283,11 +285,11 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
         if (tid < 32) {
             double v = (lane < nb) ? vec[kb + lane] : 0.0;
             for (int k = 0; k < nb; k++) {
-                if (lane == k) v = v / D[k][k];
                 const double yk = __shfl_sync(0xffffffffu, v, k);
                 if (lane > k && lane < nb) v = fma(-D[lane][k], yk, v);
             }
-            if (lane < nb) { yb[lane] = v; A.xs[f + kb + lane] = v; }
+            // y feeds the updates below; z = D^{-1} y is what the backward pass starts from
+            if (lane < nb) { yb[lane] = v; A.xs[f + kb + lane] = v / D[lane][lane]; }
         }
         __syncthreads();
         for (int i = kb + nb + tid; i < N; i += NT) {
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
     double *u = A.uv + A.sn_rowptr[s];
     for (int i = tid; i < nr; i += NT) u[i] = vec[nc + i];
 }
-// backward: x_s = L11^{-T} (y_s - L21' x_rows)
+// backward: x_s = L11^{-T} (z_s - L21' x_rows), unit diagonal
 template <int NT>
 __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
 {
@@ -331,7 +333,6 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
         if (tid < 32) {
             double v = (lane < nb) ? vec[kb + lane] : 0.0;
             for (int k = nb - 1; k >= 0; k--) {
-                if (lane == k) v = v / D[k][k];
                 const double xk = __shfl_sync(0xffffffffu, v, k);
                 if (lane < k) v = fma(-D[k][lane], xk, v);
             }

@@ -8,6 +8,7 @@
 #include <algorithm>
 
 #define LS_SMALL_MAX 2048
+#define LS_EXACT_MAX 128     // up to this many variables / breakpoints the linesearch sums run in reference order
 #define SORT_TILE 2048
 #define SORT_THREADS 256
 
@@ -71,7 +72,28 @@ __global__ void __launch_bounds__(1024) k_ls_small(LsArgs A)
         s1 += A.dy[i] * tm; s3 += A.y[i] * tm;
     }
     for (int i = tid; i < n; i += 1024) { s2 += A.dx[i] * A.Qdx[i]; s4 += A.dx[i] * A.df[i]; }
-    s1 = bsum(s1, sh); s2 = bsum(s2, sh); s3 = bsum(s3, sh); s4 = bsum(s4, sh);
+    // tiny problems: every sum in exactly the reference's scalar order (vec_prod's 4-way unrolling,
+    // lin_alg.c:59-71; vec_prod_ind, linesearch.c:190-199), so tau is bit-identical whenever dx, dy are
+    const bool exact = (n <= LS_EXACT_MAX && M2 <= LS_EXACT_MAX);
+    if (exact) {
+        if (tid < 4) {
+            const bool mvec = (tid == 0 || tid == 2);
+            const int len = mvec ? m : n;
+            double prod = 0.0;
+            int i = 0;
+            #define LS_TERM(i_) (mvec ? ((tid == 0 ? A.dy[i_] : A.y[i_]) * ((A.dy[i_] * A.mu[i_]) * 0.5)) \
+                                      : (A.dx[i_] * (tid == 1 ? A.Qdx[i_] : A.df[i_])))
+            if (len >= 4) for (; i <= len - 4; i += 4) prod += (LS_TERM(i) + LS_TERM(i + 1) + LS_TERM(i + 2) + LS_TERM(i + 3));
+            for (; i < len; i++) prod += LS_TERM(i);
+            #undef LS_TERM
+            wa[tid] = prod;
+        }
+        __syncthreads();
+        s1 = wa[0]; s2 = wa[1]; s3 = wa[2]; s4 = wa[3];
+        __syncthreads();
+    } else {
+        s1 = bsum(s1, sh); s2 = bsum(s2, sh); s3 = bsum(s3, sh); s4 = bsum(s4, sh);
+    }
     double eta = s1; eta += s2; eta *= 0.5;
     double beta = s3; beta += s4; beta *= 0.5;
     int P2 = 64; while (P2 < M2) P2 <<= 1;
@@ -82,6 +104,21 @@ __global__ void __launch_bounds__(1024) k_ls_small(LsArgs A)
     }
     aJ = bsum(aJ, sh); bJ = bsum(bJ, sh);
     const int nLt = (int)(bsum((double)nL, sh) + 0.5);
+    if (exact) {
+        __syncthreads();
+        if (tid == 0) {
+            double pa = 0.0, pb = 0.0;
+            for (int k = 0; k < M2; k++) {
+                const double dl = A.delta[k], al = A.alpha[k];
+                const bool L = (al / dl) > 0.0, P = dl > 0.0;
+                if (L != P) { pa += dl * dl; pb += dl * al; }
+            }
+            wa[0] = pa; wb[0] = pb;
+        }
+        __syncthreads();
+        aJ = wa[0]; bJ = wb[0];
+        __syncthreads();
+    }
     const double a0 = eta + aJ, b0 = beta - bJ;
     if (tid == 0) kmin = nLt;
     __syncthreads();
@@ -98,6 +135,22 @@ __global__ void __launch_bounds__(1024) k_ls_small(LsArgs A)
             }
             __syncthreads();
         }
+    if (exact) {
+        // the reference's sequential sweep, linesearch.c:121-157
+        if (tid == 0) {
+            double a = a0, b = b0, tau;
+            bool done = false;
+            if (nLt == 0 || b + a * __longlong_as_double((long long)key[0]) > 0.0) { tau = -b / a; done = true; }
+            for (int i = 0; !done && i < nLt; i++) {
+                double da, db; ls_contrib(A.delta, A.alpha, idx[i], da, db);
+                a = a + da; b = b + db;
+                if (i + 1 < nLt && b + a * __longlong_as_double((long long)key[i + 1]) > 0.0) { tau = -b / a; done = true; }
+            }
+            if (!done) tau = -b / a;
+            A.sc->tau = tau; A.sc->ls_eta = eta; A.sc->ls_beta = beta; A.sc->ls_nL = nLt;
+        }
+        return;
+    }
     // prefix sums of the slope changes in sorted order; thread owns a contiguous chunk
     const int chunk = (P2 + 1023) / 1024;             // 1 or 2
     const int k0 = tid * chunk;
