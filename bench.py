@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py -- QPDO Newton hot path on B200: KKT factor+solve ms/iter (C3) and batched QP solves/s (C5).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c3] [--impl reference]
+
+Prints ONE JSON line (rank 0).  The product arm calls only the CUDA library through the qpdo.h /
+qpdo_batch.h C ABI; oracle/ is executed only by the `cpu_baseline` leg and by `--impl reference`.
+A "step" is one pass of the hot path over one batch of synthetic input:
+  c5: solving the whole batch of MPC QPs (BASELINE.json configs[4]);  value = QP solves/s, all ranks
+  c3: one full solve of the CONT-300-shaped QP (configs[2]);          value = KKT factor+solve ms per Newton iteration
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], False
+        self.th = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 6:
+                for nm, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class Dist(object):
+    """one process per GPU; torch.distributed is plumbing (barrier + max/sum over ranks) only"""
+
+    def __init__(self, gpus, backend=None):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.td = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as td
+            self.torch, self.td = torch, td
+            if backend is None:
+                backend = "nccl" if torch.cuda.is_available() else "gloo"
+            self.backend = backend
+            if backend == "nccl":
+                torch.cuda.set_device(self.local)
+            td.init_process_group(backend=backend)
+            self.dev = torch.device("cuda", self.local) if backend == "nccl" else torch.device("cpu")
+
+    def barrier(self):
+        if self.td:
+            self.td.barrier()
+
+    def reduce(self, vals, op="max"):
+        if not self.td:
+            return list(vals)
+        t = self.torch.tensor(list(vals), dtype=self.torch.float64, device=self.dev)
+        self.td.all_reduce(t, op=self.td.ReduceOp.MAX if op == "max" else self.td.ReduceOp.SUM)
+        return t.cpu().tolist()
+
+    def gather_bytes(self, arr):
+        """all-gather equal-sized uint8 numpy arrays (status / objective summaries)"""
+        if not self.td:
+            return [arr]
+        t = self.torch.from_numpy(arr.copy()).to(self.dev)
+        outs = [self.torch.empty_like(t) for _ in range(self.world)]
+        self.td.all_gather(outs, t)
+        return [o.cpu().numpy() for o in outs]
+
+    def close(self):
+        if self.td:
+            self.td.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------ C3
+C3_N = 300
+
+
+def c3_problem(N):
+    from qpdo_b200 import problems
+    return problems.cont_like(N)
+
+
+def c3_algorithmic(info, n, m, nnzA, nnzQ):
+    """algorithmic bytes / flops per Newton iteration of the KKT phases"""
+    lnz = float(info.lnz)
+    return {"solve_bytes": 2 * (12 * lnz + 8 * n) + 16 * n,            # triangular solves, both sweeps
+            "factor_flops": float(info.flops),                        # sum_j colcount_j^2
+            "spmv_bytes": 3 * (12 * nnzA + 4 * (n + 1) + 8 * (n + m)) + (12 * nnzQ + 4 * (n + 1) + 16 * n)}
+
+
+def run_c3(args, dist):
+    import qpdo_b200
+    from qpdo_b200 import capi
+    lib = qpdo_b200.lib()
+    N = args.size or C3_N
+    p = c3_problem(N)
+    n, m = p["q"].size, p["A"].shape[0]
+    st = dict(verbose=0)
+    s = qpdo_b200.QPDO()
+    t0 = time.time()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], st)
+    setup_s = time.time() - t0
+    info = capi.DevSymbolicInfo()
+    lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
+    for _ in range(args.warmup):
+        r = s.solve()
+    prof = capi.DevProfile()
+    lib.qpdo_dev_set_profiling(s.device, 1)
+    lib.qpdo_dev_get_profile(s.device, C.byref(prof), 1)
+    dist.barrier()
+    with ClockSampler(dist.local) as clk:
+        t0 = time.time()
+        for _ in range(args.steps):
+            r = s.solve()
+        wall = time.time() - t0
+    dist.barrier()
+    lib.qpdo_dev_get_profile(s.device, C.byref(prof), 1)
+    lib.qpdo_dev_set_profiling(s.device, 0)
+    s.delete()
+    # end to end through the public API with host buffers: setup (H2D of Q, A, q, l, u + analysis) +
+    # solve (D2H of x, y, certificates) per step
+    e2e_steps = max(1, min(args.steps, 2))
+    t0 = time.time()
+    for _ in range(e2e_steps):
+        s2 = qpdo_b200.QPDO()
+        s2.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], st)
+        r2 = s2.solve()
+        s2.delete()
+    e2e_wall = (time.time() - t0) / e2e_steps
+    nnzA, nnzQ = p["A"].nnz, int(n)
+    newton = max(1, prof.n_newton)
+    kkt_ms = (prof.assemble_ms + prof.factor_ms + prof.solve_ms) / newton
+    alg = c3_algorithmic(info, n, m, nnzA, nnzQ)
+    worst = dist.reduce([kkt_ms, wall / args.steps * 1e3], "max")
+    pk, pk_src = peaks()
+    solve_ms = prof.solve_ms / newton
+    rl = {"bound": "hbm", "kernel": "supernodal triangular solves (k_fwd/k_bwd graph)", "achieved": alg["solve_bytes"] / (solve_ms * 1e-3) / 1e9,
+          "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s", "traffic": None}
+    rl["frac"] = rl["achieved"] / rl["peak"]
+    out = {"metric": "KKT factor+solve ms per Newton iteration (CONT-%d-shaped QP, n=%d m=%d)" % (N, n, m),
+           "value": worst[0], "unit": "ms/iter", "n_gpus": dist.world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": worst[1], "higher_is_better": False, "scaling": "replicas", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic", "config": {"workload": "c3: CONT-%d-like banded PDE-constraint QP, one solve per step; "
+                                           "working set (L panels + update matrices) %.0f MB vs 126 MB L2" %
+                                           (N, 8e-6 * (info.lnz_stored + info.usize)),
+                                           "N": N, "n": n, "m": m, "nnzA": int(nnzA)},
+           "phases_ms_per_newton": {"assemble": prof.assemble_ms / newton, "factor": prof.factor_ms / newton, "solve": solve_ms,
+                                    "spmv": prof.spmv_ms / newton, "linesearch": prof.linesearch_ms / newton,
+                                    "residual": prof.residual_ms / max(1, prof.n_residual), "other": prof.other_ms / newton},
+           "symbolic": {"nsuper": info.nsuper, "nlevel": info.nlevel, "max_front": info.max_front, "lnz": int(info.lnz),
+                        "lnz_stored": int(info.lnz_stored), "flops": info.flops, "analyze_s": info.analyze_seconds, "setup_s": setup_s},
+           "result": {"status": r.status_val, "iterations": r.iterations, "oterations": r.oterations, "objective": r.objective},
+           "factor_gflops": alg["factor_flops"] / (prof.factor_ms / newton * 1e-3) / 1e9,
+           "roofline": rl,
+           "e2e": {"value": e2e_wall * 1e3 / max(1, r2.iterations), "unit": "ms/iter (setup + solve wall clock / loop passes)",
+                   "h2d_bytes_per_step": int(12 * (nnzA + nnzQ) + 8 * (n + 2 * m) + 8 * (n + 1)),
+                   "d2h_bytes_per_step": int(8 * 3 * (n + m) + 8 * m), "setup_plus_solve_s": e2e_wall},
+           "gpu_launches": int(prof.kernel_launches), "clocks": clk.summary()}
+    return out
+
+
+def ref_c3(args, sample_iters=12):
+    """the unmodified reference (oracle/_ref, CHOLMOD + OpenBLAS on all host cores) on a bounded
+    sample of C3: the first `sample_iters` loop passes of the same solve"""
+    import oracle
+    from qpdo_b200 import capi
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(ncores))
+    N = args.size or C3_N
+    p = c3_problem(N)
+    kind = "reference" if oracle.have_ref() else "port"
+    t0 = time.time()
+    if kind == "reference":
+        s = capi.Solver(oracle.ref_library())
+        s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0, max_iter=sample_iters))
+        r = s.solve(); s.delete()
+        secs, iters = r.solve_time, r.iterations
+    else:
+        r = oracle.solve(p, dict(max_iter=sample_iters), trace=False)
+        secs, iters = r.solve_seconds, r.iterations
+    return {"value": secs * 1e3 / max(1, iters), "unit": "ms/iter (whole loop pass incl. factor+solve)", "cores": ncores if kind == "reference" else 1,
+            "kind": kind, "sample": "first %d loop passes of the C3 (N=%d) solve, %s" %
+            (iters, N, "CHOLMOD supernodal + OpenBLAS" if kind == "reference" else "C restatement"), "wall_s": time.time() - t0}
+
+
+# ------------------------------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=None, choices=["c3", "c5"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--size", type=int, default=0, help="c3: grid N (default 300); c5: batch size (default 65536)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    have_batch = os.path.exists(os.path.join(ROOT, "qpdo_b200", "batch.py"))
+    if args.workload is None:
+        args.workload = "c5" if have_batch else "c3"
+    if args.steps is None:
+        args.steps = 5 if args.workload == "c5" else 3
+    args.warmup = max(args.warmup, 0)
+
+    if args.impl == "reference":
+        # rank 0 alone runs the CPU reference; the other ranks exit 0 without work
+        if int(os.environ.get("RANK", "0")) != 0:
+            return 0
+        if args.workload == "c3":
+            vals = [ref_c3(args) for _ in range(max(1, min(args.steps, 2)))]
+            b = min(vals, key=lambda v: v["value"])
+            line = {"impl": "reference", "metric": "KKT factor+solve ms per Newton iteration (CONT-%d-shaped QP)" % (args.size or C3_N),
+                    "value": b["value"], "unit": "ms/iter", "higher_is_better": False}
+        else:
+            from qpdo_b200 import batch as qbatch
+            b = qbatch.bench_reference(args)
+            line = {"impl": "reference", "metric": qbatch.METRIC, "value": b["value"], "unit": "QP/s", "higher_is_better": True}
+        line.update({"n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "scaling": "strong" if args.workload == "c5" else "replicas",
+                     "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": args.workload},
+                     "cpu_baseline": b, "e2e": {"value": b["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        print(json.dumps(line))
+        return 0
+
+    dist = Dist(args.gpus)
+    try:
+        if args.workload == "c3":
+            out = run_c3(args, dist)
+        else:
+            from qpdo_b200 import batch as qbatch
+            out = qbatch.bench(args, dist, ClockSampler, peaks)
+        if dist.rank == 0:
+            if dist.world == 1 and not args.no_cpu_baseline:
+                try:
+                    if args.workload == "c3":
+                        out["cpu_baseline"] = ref_c3(args)
+                    else:
+                        out["cpu_baseline"] = qbatch.bench_reference(args, bounded=True)
+                except Exception as e:          # the baseline is a reported number, never a reason to fail the bench
+                    out["cpu_baseline"] = {"value": None, "error": repr(e)}
+            print(json.dumps(out))
+    finally:
+        dist.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -5,8 +5,8 @@ The struct layouts below are the DLONG + PROFILING layout the reference's only b
 
 This module is ABI plumbing only: it loads *a* shared library that exports the eight qpdo_*
 symbols and drives it.  The product (`qpdo_b200.QPDO`) points it at the CUDA library built from
-qpdo_b200/csrc; the tests additionally point it at oracle/_ref/libqpdo_ref*.so (the unmodified
-reference) so both are driven through byte-identical inputs.
+qpdo_b200/csrc; the tests additionally point it at a build of the unmodified reference so both
+are driven through byte-identical inputs.
 """
 import ctypes as C
 import os

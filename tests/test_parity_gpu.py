@@ -1,0 +1,194 @@
+"""GPU parity tests proper (-m gpu): the CUDA library, driven through the qpdo.h C ABI, against
+(1) the golden vectors of the unmodified reference, (2) the C restatement on fresh seeded inputs,
+(3) oracle/_ref itself when its .so travelled to the box, and (4) size-independent properties at
+BASELINE.json's full sizes."""
+import ctypes as C
+import numpy as np
+import pytest
+import scipy.sparse as sp
+from conftest import rel_err, load_golden, golden_cases
+from test_oracle import check, KNIFE_EDGE, CHAOTIC_SEQ, TOL, TOL_SEQ
+from qpdo_b200 import capi, problems
+
+pytestmark = pytest.mark.gpu
+CASES, checksum = golden_cases()
+_pd = C.POINTER(C.c_double)
+
+
+def gpu_solver():
+    import qpdo_b200
+    return qpdo_b200.QPDO()
+
+
+def gpu_solve(p, st=None, warm=None):
+    s = gpu_solver()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(dict(verbose=0), **(st or {})))
+    if warm is not None:
+        s.warm_start(*warm)
+    r = s.solve()
+    s.delete()
+    return r
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_cuda_matches_reference_golden(name):
+    gen, st = CASES[name]
+    p = gen()
+    g = load_golden(name)
+    assert checksum(p) == str(g["checksum"])
+    s = gpu_solver()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(dict(verbose=0), **st))
+    r = s.solve()
+    check(name + "/cold", g, r, "cold_", exact_iters=name not in KNIFE_EDGE)
+    if "warm_status_val" in g.files:
+        # same workspace, like the reference's demo (examples/demo_mex.m:45-53)
+        s.warm_start(g["cold_x"] * (1 + 1e-3), g["cold_y"] * (1 - 1e-3))
+        check(name + "/warm", g, s.solve(), "warm_")
+        m = p["A"].shape[0]
+        if "lams" in p:
+            xs, ys = g["cold_x"], g["cold_y"]
+            for j, lam in enumerate(p["lams"][1:], 1):
+                s.update_bounds(np.full(m, -lam), np.full(m, lam))
+                s.warm_start(xs, ys)
+                check("%s/path%d" % (name, j), g, s.solve(), "path%d_" % j)
+                xs, ys = g["path%d_x" % j], g["path%d_y" % j]
+        else:
+            s.update_bounds(p["l"] - 0.1, p["u"] + 0.05)
+            s.warm_start(g["cold_x"], g["cold_y"])
+            rb = s.solve()
+            if name in CHAOTIC_SEQ:
+                assert rb.status_val == int(g["bounds_status_val"])
+                assert abs(rb.objective - float(g["bounds_objective"])) <= 1e-6 * max(1.0, abs(float(g["bounds_objective"])))
+            else:
+                check(name + "/bounds", g, rb, "bounds_", TOL=TOL_SEQ)
+                s.update_q(p["q"] * 1.5 + 0.01)
+                check(name + "/newq", g, s.solve(), "newq_", TOL=TOL_SEQ)
+    s.delete()
+
+
+@pytest.mark.parametrize("seed", [21, 22, 23, 24])
+def test_cuda_matches_restatement_on_fresh_inputs(oracle_mod, seed):
+    p = problems.random_qp(150 + 10 * seed, 90 + seed, 0.05, seed=seed)
+    a = oracle_mod.solve(p)
+    b = gpu_solve(p)
+    assert (a.status_val, a.iterations, a.oterations) == (b.status_val, b.iterations, b.oterations)
+    assert np.array_equal(a.active_set, b.active_set)
+    assert rel_err(a.x, b.x) <= TOL and rel_err(a.y, b.y) <= TOL
+    assert abs(a.objective - b.objective) <= TOL * max(1.0, abs(a.objective))
+
+
+def test_cuda_matches_restatement_mpc_family(oracle_mod):
+    batch = problems.mpc_batch(12, first=100)
+    for i in range(12):
+        p = problems.mpc_instance(batch, i)
+        a = oracle_mod.solve(p)
+        b = gpu_solve(p)
+        assert (a.status_val, a.iterations, a.oterations) == (b.status_val, b.iterations, b.oterations), i
+        assert np.array_equal(a.active_set, b.active_set), i
+        assert rel_err(a.x, b.x) <= TOL and rel_err(a.y, b.y) <= TOL, i
+
+
+def test_cuda_matches_live_reference_when_present(oracle_mod):
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref/libqpdo_ref.so did not travel to this machine")
+    try:
+        ref = oracle_mod.ref_library()
+    except OSError as e:
+        pytest.skip("reference build not loadable here: %s" % e)
+    for nm, p in (("cont30", problems.cont_like(30)), ("rand400", problems.random_qp(400, 200, 0.02, seed=9))):
+        s = capi.Solver(ref)
+        s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+        a = s.solve(); s.delete()
+        b = gpu_solve(p)
+        assert (a.status_val, a.iterations, a.oterations) == (b.status_val, b.iterations, b.oterations), nm
+        assert np.array_equal(a.active_set, b.active_set), nm
+        assert rel_err(a.x, b.x) <= TOL and rel_err(a.y, b.y) <= TOL, nm
+
+
+def test_spmv_bit_exact_against_restatement(cuda_lib, oracle_mod):
+    """Ax, A'y, Qx follow cholmod_sdmult's accumulation order: bit-identical to the restatement."""
+    import qpdo_b200
+    L = oracle_mod.lib()
+    p = problems.random_qp(300, 200, 0.05, seed=7)
+    s = qpdo_b200.QPDO()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0, scaling=0))
+    n, m = s.n, s.m
+    Q = sp.tril(sp.csc_matrix(p["Q"]), format="csc"); Q.sort_indices()
+    A = sp.csc_matrix(p["A"]); A.sort_indices()
+    pl = C.POINTER(C.c_long)
+    rng = np.random.default_rng(0)
+    for which, M, nin, nout in ((0, A, n, m), (1, A, m, n), (2, Q, n, n)):
+        x = rng.standard_normal(nin); y = np.zeros(nout); yr = np.zeros(nout)
+        assert cuda_lib.qpdo_dev_test_spmv(s.device, which, x.ctypes.data_as(_pd), y.ctypes.data_as(_pd)) == 0
+        ip, ii = M.indptr.astype(np.int64), M.indices.astype(np.int64)
+        L.qpdo_oracle_spmv(which, M.shape[0], M.shape[1], ip.ctypes.data_as(pl), ii.ctypes.data_as(pl),
+                           M.data.ctypes.data_as(_pd), x.ctypes.data_as(_pd), yr.ctypes.data_as(_pd))
+        assert np.array_equal(y, yr), "spmv %d not bit-exact (max diff %.3e)" % (which, np.abs(y - yr).max())
+    s.delete()
+
+
+def test_ruiz_scaling_bit_exact_against_restatement(cuda_lib, oracle_mod):
+    import qpdo_b200
+    L = oracle_mod.lib()
+    p = problems.random_qp(200, 150, 0.05, seed=8)
+    s = qpdo_b200.QPDO()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+    n, m = s.n, s.m
+    Q = sp.tril(sp.csc_matrix(p["Q"]), format="csc"); Q.sort_indices()
+    A = sp.csc_matrix(p["A"]); A.sort_indices()
+    pl = C.POINTER(C.c_long)
+    Qx, Ax, q, l, u = Q.data.copy(), A.data.copy(), p["q"].copy(), p["l"].copy(), p["u"].copy()
+    D = np.zeros(n); E = np.zeros(m); c = C.c_double()
+    Qp, Qi, Ap, Ai = (a.astype(np.int64) for a in (Q.indptr, Q.indices, A.indptr, A.indices))
+    L.qpdo_oracle_scale_data(n, m, Qp.ctypes.data_as(pl), Qi.ctypes.data_as(pl), Qx.ctypes.data_as(_pd), Ap.ctypes.data_as(pl),
+                             Ai.ctypes.data_as(pl), Ax.ctypes.data_as(_pd), q.ctypes.data_as(_pd), l.ctypes.data_as(_pd),
+                             u.ctypes.data_as(_pd), 10, D.ctypes.data_as(_pd), E.ctypes.data_as(_pd), C.byref(c))
+    for nm, want in (("A_values", Ax), ("Q_values", Qx), ("q", q), ("l", l), ("u", u), ("D", D), ("E", E)):
+        got = capi.dev_vector(cuda_lib, s.device, nm, want.size)
+        assert np.array_equal(got, want), nm
+    assert s.work.scaling.contents.c == c.value
+    s.delete()
+
+
+@pytest.mark.parametrize("gen", ["rand", "cont", "lasso"])
+def test_factor_solve_residual(cuda_lib, gen):
+    """K x = b with K = Q + sigma I + A' diag(omega) A: backward error of the multifrontal LDL' + solves."""
+    import qpdo_b200
+    p = {"rand": lambda: problems.random_qp(600, 300, 0.02, seed=3), "cont": lambda: problems.cont_like(50),
+         "lasso": lambda: problems.lasso_dual(6000, 3000, window=200)}[gen]()
+    s = qpdo_b200.QPDO()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+    n, m = s.n, s.m
+    A = sp.csc_matrix(p["A"]); A.sort_indices(); A.sum_duplicates()
+    Ql = sp.tril(sp.csc_matrix(p["Q"]), format="csc"); Ql.sort_indices()
+    As = sp.csc_matrix((capi.dev_vector(cuda_lib, s.device, "A_values", A.nnz), A.indices, A.indptr), shape=A.shape)
+    Qs = sp.csc_matrix((capi.dev_vector(cuda_lib, s.device, "Q_values", Ql.nnz), Ql.indices, Ql.indptr), shape=Ql.shape)
+    Qs = Qs + sp.tril(Qs, -1).T
+    rng = np.random.default_rng(1)
+    om = rng.random(m) * (rng.random(m) < 0.5) * 10
+    sigma = 1e-3
+    K = (Qs + sigma * sp.identity(n) + As.T @ sp.diags(om) @ As).tocsc()
+    b = rng.standard_normal(n); x = np.zeros(n)
+    f, t = C.c_float(), C.c_float()
+    assert cuda_lib.qpdo_dev_test_factor_solve(s.device, om.ctypes.data_as(_pd), sigma, b.ctypes.data_as(_pd), x.ctypes.data_as(_pd),
+                                               C.byref(f), C.byref(t)) == 0, cuda_lib.qpdo_dev_last_error()
+    resid = np.abs(K @ x - b).max() / (np.abs(K).sum(axis=1).max() * np.abs(x).max() + np.abs(b).max())
+    assert resid <= 1e-12, resid
+    s.delete()
+
+
+def test_full_size_cont300_against_reference_golden(cuda_lib):
+    """BASELINE config 3 at full size (n = 90,300, m = 180,300) against the unmodified reference's
+    result (tests/golden/cont300.npz, make_golden_large.py) + KKT conditions recomputed on the host."""
+    p = problems.cont_like(300)
+    g = load_golden("cont300")
+    r = gpu_solve(p)
+    assert r.status_val == int(g["status_val"]) == 1
+    assert (r.iterations, r.oterations) == (int(g["iterations"]), int(g["oterations"]))
+    assert np.array_equal(np.packbits(r.active_set.astype(np.uint8)), g["active_set"])
+    assert rel_err(g["x"], r.x) <= TOL and rel_err(g["y"], r.y) <= TOL
+    assert abs(r.objective - float(g["objective"])) <= TOL * max(1.0, abs(float(g["objective"])))
+    A, Q = p["A"], p["Q"]
+    Ax = A @ r.x
+    assert np.abs(Ax - np.clip(Ax + r.y, p["l"], p["u"])).max() <= 1e-5
+    assert np.abs(Q @ r.x + p["q"] + A.T @ r.y).max() <= 1e-5
