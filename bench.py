@@ -141,6 +141,8 @@ def run_c3(args, dist):
     p = c3_problem(N)
     n, m = p["q"].size, p["A"].shape[0]
     st = dict(verbose=0)
+    if args.max_iter:
+        st["max_iter"] = args.max_iter
     s = qpdo_b200.QPDO()
     t0 = time.time()
     s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], st)
@@ -238,6 +240,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--size", type=int, default=0, help="c3: grid N (default 300); c5: batch size (default 65536)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--max-iter", type=int, default=0, help="c3: cap the loop passes per solve (profiling runs)")
     args = ap.parse_args()
     have_batch = os.path.exists(os.path.join(ROOT, "qpdo_b200", "batch.py"))
     if args.workload is None:

@@ -49,6 +49,7 @@ struct Factor {
 
 struct qpdo_dev {
     int n = 0, m = 0, device = 0;
+    int proximal = 1;                // settings->proximal of the running solve
     cudaStream_t st = nullptr;
     // matrices (scaled in place at setup)
     int nnzQ = 0, nnzA = 0, nnzQf = 0;

@@ -518,6 +518,7 @@ extern "C" int qpdo_dev_residuals(qpdo_dev *d, int proximal, qpdo_dev_scalars *o
 extern "C" int qpdo_dev_newton_step(qpdo_dev *d, int force_reset, int proximal)
 {
     const int n = d->n, m = d->m;
+    d->proximal = proximal;
     {
         PhaseTimer t(d, PH_OTHER);
         CUDA_OK(cudaMemsetAsync(&d->sc->n_active, 0, 3 * sizeof(int), d->st));
@@ -784,6 +785,7 @@ extern "C" int qpdo_dev_test_factor_solve(qpdo_dev *d, const double *omega, doub
     if (d->m) CUDA_OK(cudaMemcpyAsync(d->omega, omega, sizeof(double) * d->m, cudaMemcpyHostToDevice, d->st));
     CUDA_OK(cudaMemcpyAsync(d->rhs, b, sizeof(double) * d->n, cudaMemcpyHostToDevice, d->st));
     k_set_sigma<<<1, 1, 0, d->st>>>(d->sc, sigma, 0);
+    d->proximal = 1;
     cudaEventRecord(e0, d->st);
     if (factor_numeric(d)) return -1;
     cudaEventRecord(e1, d->st);

@@ -31,7 +31,7 @@ struct FArgs {
 // replacement of cholmod_aat + cholmod_add + the beta*I of cholmod_factorize_p; Lx was zeroed.
 __global__ void k_assemble_K(int64_t nnzK, const int64_t *Kdst, const int *Kq, const int64_t *Ktp, const int *Kt_row,
                              const double *Kt_val, const int *Ki, const int *Kcol, const double *Qx, const double *omega,
-                             const qpdo_dev_scalars *sc, double *Lx)
+                             const qpdo_dev_scalars *sc, int proximal, double *Lx)
 {
     int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nnzK) return;
@@ -39,7 +39,7 @@ __global__ void k_assemble_K(int64_t nnzK, const int64_t *Kdst, const int *Kq, c
     for (int64_t t = Ktp[e]; t < Ktp[e + 1]; t++) v = fma(omega[Kt_row[t]], Kt_val[t], v);
     int q = Kq[e];
     if (q >= 0) v += Qx[q];
-    if (Ki[e] == Kcol[e]) v += sc->sigma;
+    if (proximal && Ki[e] == Kcol[e]) v += sc->sigma;       // beta*I only with factorize_p (cholmod_interface.c:11-16)
     Lx[Kdst[e]] = v;
 }
 __global__ void k_products(int64_t nt, const int *a1, const int *a2, const double *Ax, double *val)
@@ -519,7 +519,7 @@ int factor_numeric(qpdo_dev *d)
         PhaseTimer t(d, PH_ASSEMBLE);
         CUDA_OK(cudaMemsetAsync(F.Lx, 0, sizeof(double) * S->lnz_stored, d->st));
         k_assemble_K<<<cdiv(S->nnzK, 256), 256, 0, d->st>>>(S->nnzK, F.Kdst, F.Kq, F.Ktp, F.Kt_row, F.Kt_val, F.Ki, F.Kcol,
-                                                            d->Qx, d->omega, d->sc, F.Lx);
+                                                            d->Qx, d->omega, d->sc, d->proximal, F.Lx);
         d->prof.kernel_launches += 2;
     }
     {
