@@ -1,0 +1,964 @@
+// batch.cu -- many independent small QPs, one CTA per QP, the whole QPDO solver in shared memory.
+//
+// Each CTA runs qpdo_setup's scaling (reference src/scaling.c:24-91), qpdo_warm_start
+// (src/qpdo.c:217-299) and the qpdo_solve loop (src/qpdo.c:304-476) for one instance: residuals and
+// norms (iteration.c:30-93, termination.c:35-77), active set / Newton direction (newton.c:13-126),
+// the regularised KKT solve K dx = rhs with K = Q + sigma I + A' diag(omega) A (replaces
+// cholmod_interface.c:8-102), exact linesearch (linesearch.c:8-158), penalty updates
+// (iteration.c:127-180) and the infeasibility certificates (termination.c:97-216).  All instances
+// share one sparsity pattern, so the fill-reducing ordering and the pattern of L are computed once
+// on the host (symbolic.cpp) and every CTA follows the same elimination program.
+//
+// Layout: per-instance inputs are instance-major in HBM (coalesced per CTA); per-CTA state is
+// ~(nnzA + nnzQ + 12 n + 16 m + n(n+1)/2) doubles of shared memory (80 KB for n=100, m=150: two CTAs
+// per SM).  K is a packed dense lower triangle in the permuted order; the linesearch scratch
+// aliases it (K is dead once dx is known).  CTAs are persistent and pull instances from an atomic
+// work queue (iteration counts are ragged).  Compiled with -fmad=false: element-wise arithmetic
+// rounds like the reference's scalar C; fma() is used only inside the factorization / solves.
+#include "dev_internal.h"
+#include "qpdo_batch.h"
+#include <algorithm>
+#include <string.h>
+#include <vector>
+
+#define BNT 256                 // threads per CTA
+#define BNW (BNT / 32)
+#define B_INFTY 1e20
+#define LS_EXACT_MAX 128        // same threshold as linesearch.cu
+
+struct BatchPlan {
+    int n, m, nnzA, nnzQ, nnzK, nKpack, karea, P2;
+    // shared structure (device pointers)
+    const int *Ap, *Ai;                      // CSC of A
+    const int *Rp, *Rj, *Rsrc;               // CSR of A (Rsrc: index into the CSC values)
+    const int *Qp, *Qi;                      // lower CSC of Q
+    const int *Fp, *Fj, *Fsrc, *Fdiag;       // full symmetric CSR of Q (split point per row)
+    const int *perm;                         // perm[new] = old
+    const int *Kpos, *Kq, *Ktp, *Kt_row, *Kt_a1, *Kt_a2;     // K entries -> packed position, sources
+    const unsigned char *Kdiag;
+    const int *Lcp, *Lri;                    // L column patterns (rows strictly below the diagonal)
+    const int *Lrp, *Lci;                    // L row patterns (columns strictly left of the diagonal)
+    // settings (reference include/types.h:96-116)
+    int max_iter, inner_max_iter, proximal, scaling, reset_newton_iter;
+    double eps_abs, eps_abs_in, eps_prim_inf, eps_dual_inf, rho, theta, delta, mu_min, sigma_init, sigma_upd, sigma_min;
+};
+
+struct BatchIO {
+    const double *Qx, *Ax, *q, *l, *u, *c, *x0, *y0;
+    double *x, *y;
+    qpdo_batch_summary *summary;
+    unsigned char *active;
+    int count;
+    int *next;                               // work queue head
+};
+
+// ------------------------------------------------------------------------------- block reductions
+template <int K> __device__ __forceinline__ void block_max(double (&v)[K], double *red)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < K; k++)
+        for (int o = 16; o; o >>= 1) { double t = __shfl_xor_sync(0xffffffffu, v[k], o); v[k] = t > v[k] ? t : v[k]; }
+    __syncthreads();
+    if (lane == 0)
+#pragma unroll
+        for (int k = 0; k < K; k++) red[wid * K + k] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        double mx = red[k];
+        for (int w = 1; w < BNW; w++) { double t = red[w * K + k]; mx = t > mx ? t : mx; }
+        v[k] = mx;
+    }
+}
+// fixed-shape sum: xor tree inside warps, then the warp partials in index order (deterministic)
+template <int K> __device__ __forceinline__ void block_sum(double (&v)[K], double *red)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < K; k++)
+        for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    __syncthreads();
+    if (lane == 0)
+#pragma unroll
+        for (int k = 0; k < K; k++) red[wid * K + k] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        double s = 0.0;
+        for (int w = 0; w < BNW; w++) s += red[w * K + k];
+        v[k] = s;
+    }
+}
+__device__ __forceinline__ int block_count3(int a, int b, int c, int &oa, int &ob, int &oc, double *red)
+{
+    unsigned ba = __ballot_sync(0xffffffffu, a), bb = __ballot_sync(0xffffffffu, b), bc = __ballot_sync(0xffffffffu, c);
+    int *ri = (int *)red;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) { ri[wid * 3] = __popc(ba); ri[wid * 3 + 1] = __popc(bb); ri[wid * 3 + 2] = __popc(bc); }
+    __syncthreads();
+    oa = ob = oc = 0;
+    for (int w = 0; w < BNW; w++) { oa += ri[w * 3]; ob += ri[w * 3 + 1]; oc += ri[w * 3 + 2]; }
+    return oa;
+}
+__device__ __forceinline__ double bclamp(double a, double lo, double hi)
+{   // c_max(bmin, c_min(a, bmax))  (lin_alg.c:163-168)
+    double t = a < hi ? a : hi;
+    return lo > t ? lo : t;
+}
+
+// ------------------------------------------------------------------------------- SpMV (cholmod_sdmult order)
+__device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, const double *x, double *y)
+{   // CSR gather in ascending column order == CSC scatter order (t_cholmod_sdmult.c:297-320)
+    for (int i = threadIdx.x; i < P.m; i += BNT) {
+        double s = 0.0;
+        for (int k = P.Rp[i]; k < P.Rp[i + 1]; k++) s += Av[P.Rsrc[k]] * x[P.Rj[k]];
+        y[i] = s;
+    }
+}
+__device__ __forceinline__ void b_spmv_At(const BatchPlan &P, const double *Av, const double *x, double *y)
+{   // t_cholmod_sdmult.c:141-165
+    for (int j = threadIdx.x; j < P.n; j += BNT) {
+        double s = 0.0;
+        for (int k = P.Ap[j]; k < P.Ap[j + 1]; k++) s += Av[k] * x[P.Ai[k]];
+        y[j] = s;
+    }
+}
+__device__ __forceinline__ void b_spmv_Q(const BatchPlan &P, const double *Qv, const double *x, double *y)
+{   // t_cholmod_sdmult.c:440-484 (split sum)
+    for (int i = threadIdx.x; i < P.n; i += BNT) {
+        const int b = P.Fp[i], mid = b + P.Fdiag[i], e = P.Fp[i + 1];
+        double s1 = 0.0, s2 = 0.0;
+        for (int k = b; k < mid; k++) s1 += Qv[P.Fsrc[k]] * x[P.Fj[k]];
+        for (int k = mid; k < e; k++) s2 += Qv[P.Fsrc[k]] * x[P.Fj[k]];
+        y[i] = s1 + s2;
+    }
+}
+
+// ------------------------------------------------------------------------------- KKT matrix, LDL', solves
+__device__ __forceinline__ int koff(int j, int n) { return j * n - ((j * (j - 1)) >> 1) - j; }   // (i, j), i >= j, at koff(j) + i
+
+// K = Q + sigma I + A' diag(omega) A in the permuted packed lower triangle: the fused replacement
+// of cholmod_aat + cholmod_add + beta*I (cholmod_interface.c:11-16,45-48); same per-entry
+// arithmetic as k_assemble_K of factor.cu
+__device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av, const double *Qv, const double *om,
+                                           double sigma, double *K)
+{
+    for (int t = threadIdx.x; t < P.nKpack; t += BNT) K[t] = 0.0;
+    __syncthreads();
+    for (int e = threadIdx.x; e < P.nnzK; e += BNT) {
+        double v = 0.0;
+        for (int t = P.Ktp[e]; t < P.Ktp[e + 1]; t++) v = fma(om[P.Kt_row[t]], Av[P.Kt_a1[t]] * Av[P.Kt_a2[t]], v);
+        const int q = P.Kq[e];
+        if (q >= 0) v += Qv[q];
+        if (P.proximal && P.Kdiag[e]) v += sigma;
+        K[P.Kpos[e]] = v;
+    }
+    __syncthreads();
+}
+
+// Right-looking LDL' following the precomputed pattern of L; the right-hand side rides along as an
+// extra row, so the forward solve costs no extra synchronisation.  On return K holds unit L and D,
+// xs = D^{-1} L^{-1} xs_in.  One __syncthreads per column.
+__device__ __forceinline__ void b_factor_forward(const BatchPlan &P, double *K, double *xs)
+{
+    const int n = P.n, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int k = 0; k < n; k++) {
+        const int ck = koff(k, n);
+        const double dk = K[ck + k];
+        const int rb = P.Lcp[k], nr = P.Lcp[k + 1] - rb;
+        const int *R = P.Lri + rb;
+        const double xk = xs[k];
+        for (int b = wid; b < nr; b += BNW) {
+            const int rj = R[b];
+            const double ljk = K[ck + rj] / dk;
+            const int cj = koff(rj, n);
+            for (int a = b + lane; a < nr; a += 32) { const int ri = R[a]; K[cj + ri] = fma(-K[ck + ri], ljk, K[cj + ri]); }
+            if (lane == 31) xs[rj] = fma(-ljk, xk, xs[rj]);
+        }
+        __syncthreads();
+        for (int a = threadIdx.x; a < nr; a += BNT) K[ck + R[a]] = K[ck + R[a]] / dk;
+        if (threadIdx.x == BNT - 1) xs[k] = xk / dk;
+    }
+    __syncthreads();
+}
+// x = L^{-T} xs, row-oriented scatter (no reductions), one warp
+__device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, double *xs)
+{
+    const int n = P.n, lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) {
+        for (int i = n - 1; i > 0; i--) {
+            const double xi = xs[i];
+            const int cb = P.Lrp[i], nc = P.Lrp[i + 1] - cb;
+            for (int t = lane; t < nc; t += 32) { const int k = P.Lci[cb + t]; xs[k] = fma(-K[koff(k, n) + i], xi, xs[k]); }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------------------- exact linesearch
+// reference src/linesearch.c:8-158; the CTA-wide version of k_ls_small (linesearch.cu): breakpoints
+// t_i = alpha_i / delta_i, keep t_i > 0, bitonic sort of (IEEE bits, index) in shared memory, prefix
+// sums of the slope changes, first segment whose end has a positive derivative.
+struct BVec {       // shared-memory vectors of one instance
+    double *Av, *Qv, *q, *x, *xbar, *Qx, *Aty, *dx, *Qdx, *Atdy, *df, *rdi, *tn, *D;
+    double *l, *u, *y, *ybar, *Ax, *dy, *Adx, *w, *rp, *rpo, *rpi, *mu, *smu, *om, *E, *tm;
+    double *K, *red;
+    unsigned char *act, *acto;
+};
+__device__ __forceinline__ void b_ls_contrib(const double *delta, const double *alpha, int iz, double &da, double &db)
+{   // linesearch.c:133-141
+    const double d = delta[iz], al = alpha[iz];
+    if (d > 0.0) { da = d * d; db = -(d * al); }
+    else { da = -(d * d); db = d * al; }
+}
+__device__ double b_linesearch(const BatchPlan &P, const BVec &V)
+{
+    const int tid = threadIdx.x, n = P.n, m = P.m, M2 = 2 * m, P2 = P.P2, lane = tid & 31, wid = tid >> 5;
+    double *delta = V.K, *alpha = V.K + M2;
+    unsigned long long *key = (unsigned long long *)(V.K + 2 * M2);
+    int *idx = (int *)(key + P2);
+    double *red = V.red;
+    __shared__ int kmin;
+    __shared__ double wa[BNW], wb[BNW], tau_sh;
+    double s[4] = {0, 0, 0, 0};
+    for (int i = tid; i < m; i += BNT) {
+        double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
+        s[0] += V.dy[i] * tm; s[2] += V.y[i] * tm;
+    }
+    for (int i = tid; i < n; i += BNT) { s[1] += V.dx[i] * V.Qdx[i]; s[3] += V.dx[i] * V.df[i]; }
+    const bool exact = (n <= LS_EXACT_MAX && M2 <= LS_EXACT_MAX);
+    if (exact) {
+        // tiny problems: every sum in the reference's scalar order (vec_prod, lin_alg.c:59-71)
+        __syncthreads();
+        if (tid < 4) {
+            const bool mvec = (tid == 0 || tid == 2);
+            const int len = mvec ? m : n;
+            double prod = 0.0;
+            int i = 0;
+            #define LS_TERM(i_) (mvec ? ((tid == 0 ? V.dy[i_] : V.y[i_]) * ((V.dy[i_] * V.mu[i_]) * 0.5)) \
+                                      : (V.dx[i_] * (tid == 1 ? V.Qdx[i_] : V.df[i_])))
+            if (len >= 4) for (; i <= len - 4; i += 4) prod += (LS_TERM(i) + LS_TERM(i + 1) + LS_TERM(i + 2) + LS_TERM(i + 3));
+            for (; i < len; i++) prod += LS_TERM(i);
+            #undef LS_TERM
+            red[tid] = prod;
+        }
+        __syncthreads();
+        s[0] = red[0]; s[1] = red[1]; s[2] = red[2]; s[3] = red[3];
+        __syncthreads();
+    } else block_sum<4>(s, red);
+    double eta = s[0]; eta += s[1]; eta *= 0.5;
+    double beta = s[2]; beta += s[3]; beta *= 0.5;
+    double r3[3] = {0, 0, 0};                  // aJ, bJ, nL
+    for (int k = tid; k < P2; k += BNT) {
+        if (k < M2) {                          // linesearch.c:28-39,82-114
+            const int i = k < m ? k : k - m;
+            double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
+            double c0 = V.Adx[i] + (-1.0) * tm;
+            double dl = c0 * V.smu[i], al;
+            if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
+            else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
+            delta[k] = dl; alpha[k] = al;
+            const double t = al / dl;
+            const bool L = t > 0.0, Pp = dl > 0.0;
+            if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
+            if (L) { r3[2] += 1.0; key[k] = (unsigned long long)__double_as_longlong(t); }
+            else key[k] = ~0ull;
+            idx[k] = k;
+        } else { key[k] = ~0ull; idx[k] = 0; }
+    }
+    block_sum<3>(r3, red);
+    const int nLt = (int)(r3[2] + 0.5);
+    double aJ = r3[0], bJ = r3[1];
+    if (exact) {
+        if (tid == 0) {                        // vec_prod_ind, linesearch.c:190-199
+            double pa = 0.0, pb = 0.0;
+            for (int k = 0; k < M2; k++) {
+                const double dl = delta[k], al = alpha[k];
+                const bool L = (al / dl) > 0.0, Pp = dl > 0.0;
+                if (L != Pp) { pa += dl * dl; pb += dl * al; }
+            }
+            wa[0] = pa; wb[0] = pb;
+        }
+        __syncthreads();
+        aJ = wa[0]; bJ = wb[0];
+        __syncthreads();
+    }
+    const double a0 = eta + aJ, b0 = beta - bJ;
+    if (tid == 0) kmin = nLt;
+    __syncthreads();
+    for (int size = 2; size <= P2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = tid; t < (P2 >> 1); t += BNT) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool up = ((lo & size) == 0);
+                const unsigned long long ka = key[lo], kb = key[hi];
+                const int ia = idx[lo], ib = idx[hi];
+                const bool gt = (ka > kb) || (ka == kb && ia > ib);
+                if (gt == up) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
+            }
+            __syncthreads();
+        }
+    if (exact) {                               // the reference's sequential sweep, linesearch.c:121-157
+        if (tid == 0) {
+            double a = a0, b = b0, tau = 0.0;
+            bool done = false;
+            if (nLt == 0 || b + a * __longlong_as_double((long long)key[0]) > 0.0) { tau = -b / a; done = true; }
+            for (int i = 0; !done && i < nLt; i++) {
+                double da, db; b_ls_contrib(delta, alpha, idx[i], da, db);
+                a = a + da; b = b + db;
+                if (i + 1 < nLt && b + a * __longlong_as_double((long long)key[i + 1]) > 0.0) { tau = -b / a; done = true; }
+            }
+            if (!done) tau = -b / a;
+            tau_sh = tau;
+        }
+        __syncthreads();
+        return tau_sh;
+    }
+    const int chunk = (P2 + BNT - 1) / BNT, k0 = tid * chunk;
+    double la = 0, lb = 0;
+    for (int c = 0; c < chunk; c++) {
+        const int k = k0 + c;
+        if (k < nLt) { double da, db; b_ls_contrib(delta, alpha, idx[k], da, db); la += da; lb += db; }
+    }
+    double pa = la, pb = lb;
+    for (int o = 1; o < 32; o <<= 1) {
+        double ta = __shfl_up_sync(0xffffffffu, pa, o), tb = __shfl_up_sync(0xffffffffu, pb, o);
+        if (lane >= o) { pa += ta; pb += tb; }
+    }
+    if (lane == 31) { wa[wid] = pa; wb[wid] = pb; }
+    __syncthreads();
+    double oa = 0, ob = 0;
+    for (int w = 0; w < wid; w++) { oa += wa[w]; ob += wb[w]; }
+    double ra = a0 + (oa + pa - la), rb = b0 + (ob + pb - lb);
+    double cand_a = 0, cand_b = 0; int cand_k = -1;
+    for (int c = 0; c < chunk; c++) {
+        const int k = k0 + c;
+        if (k < nLt) {
+            const double t = __longlong_as_double((long long)key[k]);
+            if (cand_k < 0 && rb + ra * t > 0.0) { cand_k = k; cand_a = ra; cand_b = rb; }
+            double da, db; b_ls_contrib(delta, alpha, idx[k], da, db);
+            ra += da; rb += db;
+        }
+    }
+    if (cand_k >= 0) atomicMin(&kmin, cand_k);
+    __syncthreads();
+    if (cand_k >= 0 && cand_k == kmin) tau_sh = -cand_b / cand_a;
+    if (kmin == nLt && tid == 0) {             // no crossing before the last breakpoint (linesearch.c:148-156)
+        double ta = 0, tb = 0;
+        for (int w = 0; w < BNW; w++) { ta += wa[w]; tb += wb[w]; }
+        tau_sh = -(b0 + tb) / (a0 + ta);
+    }
+    __syncthreads();
+    return tau_sh;
+}
+
+// ------------------------------------------------------------------------------- one instance
+#define FOR_N(i) for (int i = threadIdx.x; i < n; i += BNT)
+#define FOR_M(i) for (int i = threadIdx.x; i < m; i += BNT)
+
+__device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BVec &V, const int b)
+{
+    const int n = P.n, m = P.m, tid = threadIdx.x;
+    const bool scaled = P.scaling > 0, proximal = P.proximal != 0;
+    double *red = V.red;
+    // ---- load (qpdo_setup's deep copy, src/qpdo.c:100-109); infinite bounds clipped like qpdo.m:138-139
+    for (int k = tid; k < P.nnzA; k += BNT) V.Av[k] = io.Ax[(size_t)b * P.nnzA + k];
+    for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = io.Qx[(size_t)b * P.nnzQ + k];
+    FOR_N(i) { V.q[i] = io.q[(size_t)b * n + i]; V.x[i] = 0.0; V.xbar[i] = 0.0; V.Qx[i] = 0.0; V.Aty[i] = 0.0; V.D[i] = 1.0; V.dx[i] = 0.0; }
+    FOR_M(i) {
+        double lo = io.l[(size_t)b * m + i], hi = io.u[(size_t)b * m + i];
+        V.l[i] = lo > -B_INFTY ? lo : -B_INFTY; V.u[i] = hi < B_INFTY ? hi : B_INFTY;
+        V.y[i] = 0.0; V.ybar[i] = 0.0; V.Ax[i] = 0.0; V.E[i] = 1.0; V.om[i] = 0.0; V.dy[i] = 0.0; V.rpo[i] = 0.0;
+        V.act[i] = 0; V.acto[i] = 0;
+    }
+    double c = 1.0, cinv = 1.0;
+    __syncthreads();
+    // ---- scale_data (src/scaling.c:24-91): Ruiz sweeps on A, Q <- DQD, q <- Dq, cost scaling
+    if (scaled) {
+        for (int it = 0; it < P.scaling; it++) {
+            FOR_N(j) { double mx = 0.0; for (int k = P.Ap[j]; k < P.Ap[j + 1]; k++) { double v = fabs(V.Av[k]); mx = v > mx ? v : mx; } V.tn[j] = mx; }
+            FOR_M(i) { double mx = 0.0; for (int k = P.Rp[i]; k < P.Rp[i + 1]; k++) { double v = fabs(V.Av[P.Rsrc[k]]); mx = v > mx ? v : mx; } V.tm[i] = mx; }
+            FOR_N(j) { double v = V.tn[j]; v = v < 1e-9 ? 1.0 : v; v = sqrt(v); v = 1.0 / v; V.tn[j] = v; V.D[j] = V.D[j] * v; }
+            FOR_M(i) { double v = V.tm[i]; v = v < 1e-9 ? 1.0 : v; v = sqrt(v); v = 1.0 / v; V.tm[i] = v; V.E[i] = V.E[i] * v; }
+            __syncthreads();
+            FOR_N(j) { const double dj = V.tn[j]; for (int k = P.Ap[j]; k < P.Ap[j + 1]; k++) { double v = V.Av[k] * V.tm[P.Ai[k]]; V.Av[k] = v * dj; } }
+            __syncthreads();
+        }
+        FOR_N(j) { const double t = V.D[j]; for (int k = P.Qp[j]; k < P.Qp[j + 1]; k++) { double f = t * V.D[P.Qi[k]]; V.Qv[k] = V.Qv[k] * f; } }
+        double nq[1] = {0.0};
+        FOR_N(i) { double v = V.D[i] * V.q[i]; V.q[i] = v; double t = 0.0 + 1.0 * v; t = fabs(t); nq[0] = t > nq[0] ? t : nq[0]; }
+        block_max<1>(nq, red);
+        c = 1.0 / (nq[0] > 1.0 ? nq[0] : 1.0);
+        cinv = 1.0 / c;
+        FOR_N(i) V.q[i] = V.q[i] * c;
+        for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = V.Qv[k] * c;
+        FOR_M(i) { V.l[i] = V.E[i] * V.l[i]; V.u[i] = V.E[i] * V.u[i]; }
+        __syncthreads();
+    }
+    // ---- qpdo_warm_start (src/qpdo.c:217-299)
+    double sigma = P.sigma_init;
+    if (io.x0) {
+        FOR_N(i) { double v = io.x0[(size_t)b * n + i]; if (scaled) v = v * (1.0 / V.D[i]); V.x[i] = v; V.xbar[i] = v; V.dx[i] = v; }
+        __syncthreads();
+        b_spmv_Q(P, V.Qv, V.dx, V.Qdx);
+        b_spmv_A(P, V.Av, V.dx, V.Adx);
+        __syncthreads();
+        FOR_N(i) V.Qx[i] = proximal ? V.Qdx[i] + sigma * V.x[i] : V.Qdx[i];
+        FOR_M(i) V.Ax[i] = V.Adx[i];
+    }
+    if (io.y0) {
+        FOR_M(i) { double v = io.y0[(size_t)b * m + i]; if (scaled) { v = v * (1.0 / V.E[i]); v = v * c; } V.y[i] = v; V.ybar[i] = v; V.dy[i] = v; }
+        __syncthreads();
+        b_spmv_At(P, V.Av, V.dy, V.Atdy);
+        __syncthreads();
+        FOR_N(i) V.Aty[i] = V.Atdy[i];
+    }
+    __syncthreads();
+    {   // initialize_mu (src/iteration.c:98-122)
+        double d2[2] = {0.0, 0.0};
+        FOR_N(i) { d2[0] += V.x[i] * V.Qx[i]; d2[1] += V.q[i] * V.x[i]; }
+        block_sum<2>(d2, red);
+        const double f = 0.5 * d2[0] + d2[1];
+        FOR_M(i) {
+            double z = bclamp(V.Ax[i], V.l[i], V.u[i]);
+            double t = V.Ax[i] + (-1.0) * z;
+            double num = 0.5 * t * t; num = num > 1.0 ? num : 1.0;
+            double den = fabs(f); den = den > 1.0 ? den : 1.0;
+            double v = 0.1 * num / den; v = v < 1e3 ? v : 1e3; v = v > 1e-3 ? v : 1e-3;
+            V.mu[i] = v; V.smu[i] = 1.0 / sqrt(v);
+        }
+    }
+    const double sqrt_mu_min = 1.0 / sqrt(P.mu_min);
+    // ---- qpdo_solve (src/qpdo.c:304-476)
+    double eps_in = P.eps_abs_in, tau = 0.0;
+    sigma = P.sigma_init;
+    int reset_newton = 1, iter, oter = 0, iter_old = 0, status = QPDO_UNSOLVED, n_active = 0;
+    double rpn = 0, rdn = 0, rpin = 0, rdin = 0;
+    __syncthreads();
+    for (iter = 0; iter < P.max_iter; iter++) {
+        {   // compute_outer/inner_residuals (+_norm): iteration.c:30-93, termination.c:35-77
+            double nr[4] = {0, 0, 0, 0};
+            FOR_M(i) {
+                const double Ax = V.Ax[i], y = V.y[i], l = V.l[i], u = V.u[i], mu = V.mu[i], yb = V.ybar[i];
+                double t;
+                if (scaled) { const double E = V.E[i]; t = E * y; t = t * cinv; t = E * t; t = Ax + t; } else t = Ax + y;
+                t = bclamp(t, l, u);
+                const double rp = Ax + (-1.0) * t;
+                V.rp[i] = rp;
+                const double w = Ax + mu * (yb - 0.5 * y);
+                V.w[i] = w;
+                const double z = bclamp(w, l, u);
+                const double rpi = Ax + mu * (yb - y) - z;
+                V.rpi[i] = rpi;
+                const double Einv = scaled ? 1.0 / V.E[i] : 1.0;
+                double a = fabs(scaled ? Einv * rp : rp), bb = fabs(scaled ? Einv * rpi : rpi);
+                nr[0] = a > nr[0] ? a : nr[0]; nr[1] = bb > nr[1] ? bb : nr[1];
+            }
+            FOR_N(i) {
+                double df = V.Qx[i] + V.q[i], rd;
+                if (proximal) { rd = df + (-sigma) * V.x[i]; rd = rd + V.Aty[i]; } else rd = df + V.Aty[i];
+                if (proximal) df = df + (-sigma) * V.xbar[i];
+                V.df[i] = df;
+                const double rdi = df + V.Aty[i];
+                V.rdi[i] = rdi;
+                const double Dinv = scaled ? 1.0 / V.D[i] : 1.0;
+                double a = fabs(scaled ? Dinv * rd : rd), bb = fabs(scaled ? Dinv * rdi : rdi);
+                nr[2] = a > nr[2] ? a : nr[2]; nr[3] = bb > nr[3] ? bb : nr[3];
+            }
+            block_max<4>(nr, red);
+            rpn = nr[0]; rpin = nr[1]; rdn = nr[2]; rdin = nr[3];
+            if (scaled) { rdn = rdn * cinv; rdin = rdin * cinv; }
+        }
+        // check_outer_optimality (termination.c:11-23)
+        if (rpn > B_INFTY || rdn > B_INFTY) { status = QPDO_NON_CVX; break; }
+        if (rpn <= P.eps_abs && rdn <= P.eps_abs) { status = QPDO_SOLVED; break; }
+        if (((iter > iter_old + 1) && (rpin <= eps_in) && (rdin <= eps_in)) || (iter == iter_old + P.inner_max_iter)) {
+            if (iter < iter_old + P.inner_max_iter) {
+                if (P.eps_prim_inf > 0) {      // qpdo.c:370-379 + is_primal_infeasible (termination.c:97-151)
+                    double nd[1] = {0.0};
+                    FOR_M(i) { double v = V.y[i] + (-1.0) * V.ybar[i]; V.dy[i] = v; double t = fabs(scaled ? v * V.E[i] : v); nd[0] = t > nd[0] ? t : nd[0]; }
+                    block_max<1>(nd, red);
+                    b_spmv_At(P, V.Av, V.dy, V.Atdy);
+                    const double en = P.eps_prim_inf * nd[0];
+                    __syncthreads();
+                    if (en != 0) {
+                        double s1[1] = {0.0}, mx[1] = {0.0};
+                        FOR_M(i) {
+                            const double lim = scaled ? V.E[i] * 1e20 : 1e20, d = V.dy[i];
+                            const double dp = d > 0.0 ? d : 0.0, dm = d < 0.0 ? d : 0.0;
+                            s1[0] += (V.u[i] < lim) ? V.u[i] * dp : 0.0;
+                            s1[0] += (V.l[i] > -lim) ? V.l[i] * dm : 0.0;
+                        }
+                        FOR_N(i) { double v = V.Atdy[i]; if (scaled) { v = (1.0 / V.D[i]) * v; V.Atdy[i] = v; } v = fabs(v); mx[0] = v > mx[0] ? v : mx[0]; }
+                        block_sum<1>(s1, red);
+                        block_max<1>(mx, red);
+                        if (mx[0] <= en && s1[0] <= -en) {
+                            status = QPDO_PRIMAL_INFEASIBLE;
+                            if (scaled) { FOR_M(i) { double v = V.dy[i] * cinv; V.dy[i] = V.E[i] * v; } }
+                            break;
+                        }
+                    }
+                }
+                if (P.eps_dual_inf > 0) {      // qpdo.c:381-392 + is_dual_infeasible (termination.c:156-216)
+                    double nd[1] = {0.0};
+                    FOR_N(i) { double v = V.x[i] + (-1.0) * V.xbar[i]; V.dx[i] = v; double t = fabs(scaled ? v * V.D[i] : v); nd[0] = t > nd[0] ? t : nd[0]; }
+                    block_max<1>(nd, red);
+                    b_spmv_Q(P, V.Qv, V.dx, V.Qdx);
+                    b_spmv_A(P, V.Av, V.dx, V.Adx);
+                    const double en = P.eps_dual_inf * nd[0];
+                    __syncthreads();
+                    if (en != 0) {
+                        int viol = 0, d1, d2;
+                        FOR_M(k) {
+                            double a = V.Adx[k];
+                            if (scaled) { a = (1.0 / V.E[k]) * a; V.Adx[k] = a; }
+                            const double lim = scaled ? V.E[k] * 1e20 : 1e20;
+                            if ((V.u[k] < lim && a >= en) || (V.l[k] > -lim && a <= -en)) viol = 1;
+                        }
+                        block_count3(viol, 0, 0, viol, d1, d2, red);
+                        if (!viol) {
+                            double mx[1] = {0.0}, dt[1] = {0.0};
+                            const double sv = sigma * (-tau);
+                            FOR_N(i) {
+                                double v = V.Qdx[i];
+                                if (proximal) { v = v + sv * V.dx[i]; V.Qdx[i] = v; }
+                                v = fabs(v); mx[0] = v > mx[0] ? v : mx[0];
+                                dt[0] += V.q[i] * V.dx[i];
+                            }
+                            block_max<1>(mx, red);
+                            block_sum<1>(dt, red);
+                            const double lim = scaled ? c * en : en;
+                            if (mx[0] <= lim && dt[0] <= -lim) {
+                                status = QPDO_DUAL_INFEASIBLE;
+                                if (scaled) { FOR_N(i) V.dx[i] = V.D[i] * V.dx[i]; }
+                                break;
+                            }
+                        }
+                    }
+                }
+            }
+            // outer update (qpdo.c:396-430)
+            FOR_N(i) V.xbar[i] = V.x[i];
+            FOR_M(i) V.ybar[i] = V.y[i];
+            if (oter > 0 && rpn > P.eps_abs) {                         // update_mu (iteration.c:127-168)
+                double nm[1] = {0.0};
+                FOR_M(i) { double t = fabs(V.rp[i]); nm[0] = t > nm[0] ? t : nm[0]; }
+                block_max<1>(nm, red);
+                int changed_any = 0;
+                FOR_M(k) {
+                    const double r = fabs(V.rp[k]), ro = fabs(V.rpo[k]);
+                    double thr = P.theta * ro; thr = P.eps_abs > thr ? P.eps_abs : thr;
+                    double dw = 0.0;
+                    if (r > thr) {
+                        double t = P.delta * nm[0] / r; t = t < 1.0 ? t : 1.0;
+                        const double mu_factor = 1.0 / t, mu_old = V.mu[k], mu_new = mu_old / mu_factor;
+                        double s; int changed;
+                        if (mu_new >= P.mu_min) { changed = (mu_old != mu_new); V.mu[k] = mu_new; s = sqrt(mu_factor); V.smu[k] = s * V.smu[k]; }
+                        else { changed = (mu_old != P.mu_min); V.mu[k] = P.mu_min; s = sqrt_mu_min / V.smu[k]; V.smu[k] = sqrt_mu_min; }
+                        if (changed) { const double f = sqrt(1.0 - 1.0 / (s * s)); const double col = V.smu[k] * f; dw = col * col; changed_any++; }
+                    }
+                    V.tm[k] = dw;
+                }
+                int nch, d1, d2;
+                {   // count over the CTA (a thread may own several rows)
+                    double cs[1] = {(double)changed_any};
+                    block_sum<1>(cs, red);
+                    nch = (int)(cs[0] + 0.5); (void)d1; (void)d2;
+                }
+                if ((proximal && sigma > P.sigma_min) || nch > 25) reset_newton = 1;
+                else if (nch) { FOR_M(k) V.om[k] = V.om[k] + V.tm[k]; }      // ldlupdate_mu_changed (cholmod_interface.c:77-93)
+            }
+            if (proximal && oter > 0 && rdn > P.eps_abs && sigma > P.sigma_min) {      // update_sigma (iteration.c:173-180)
+                const double s_old = sigma;
+                double s_new = s_old * P.sigma_upd; s_new = s_new > P.sigma_min ? s_new : P.sigma_min;
+                sigma = s_new; reset_newton = 1;
+                const double ds = s_new - s_old;
+                FOR_N(i) V.Qx[i] = V.Qx[i] + ds * V.x[i];
+            }
+            if (iter < iter_old + P.inner_max_iter) { const double e1 = P.rho * eps_in, e2 = 0.1 * P.eps_abs; eps_in = e1 > e2 ? e1 : e2; }
+            FOR_M(i) V.rpo[i] = V.rp[i];
+            oter++; iter_old = iter;
+            __syncthreads();
+        } else {
+            // ---- update_iterate (iteration.c:11-25): newton_direction (newton.c:13-91)
+            if (P.reset_newton_iter != 0 && iter % P.reset_newton_iter == 0) reset_newton = 1;
+            int ca = 0, ce = 0, cl = 0, n_enter, n_leave;
+            FOR_M(i) {
+                const double wi = V.w[i];
+                const int a = (wi <= V.l[i]) || (wi >= V.u[i]), o = V.acto[i];
+                V.act[i] = (unsigned char)a;
+                ca += a; ce += (a && !o); cl += (!a && o);
+            }
+            {
+                double cs[3] = {(double)ca, (double)ce, (double)cl};
+                block_sum<3>(cs, red);
+                n_active = (int)(cs[0] + 0.5); n_enter = (int)(cs[1] + 0.5); n_leave = (int)(cs[2] + 0.5);
+            }
+            int mode;
+            if ((reset_newton && n_active) || (n_enter + n_leave) > QPDO_MAX_RANK_UPDATE) { mode = 0; reset_newton = 0; }
+            else if (n_active) mode = 1;
+            else mode = 2;
+            FOR_M(i) {      // row weights embodied in the factor + "dy" = (I+P) res_prim_in ./ mu (newton.c:37-40)
+                const int a = V.act[i], o = V.acto[i];
+                const double inv = 1.0 / V.mu[i];
+                double om;
+                if (mode == 0) om = a ? inv : 0.0;
+                else if (mode == 1) { om = V.om[i]; if (a && !o) om = om + inv; if (!a && o) om = om - inv; }
+                else om = 0.0;
+                V.om[i] = om;
+                V.acto[i] = (unsigned char)a;
+                double v = V.rpi[i] / V.mu[i];
+                if (!a) v = v * 2.0;
+                V.dy[i] = v;
+            }
+            __syncthreads();
+            b_spmv_At(P, V.Av, V.dy, V.Atdy);
+            b_assemble(P, V.Av, V.Qv, V.om, sigma, V.K);            // ends with __syncthreads
+            FOR_N(k) { const int o = P.perm[k]; V.tn[k] = -V.rdi[o] - V.Atdy[o]; }     // P * rhs (newton.c:43-45)
+            __syncthreads();
+            b_factor_forward(P, V.K, V.tn);
+            b_backward(P, V.K, V.tn);
+            FOR_N(k) V.dx[P.perm[k]] = V.tn[k];
+            __syncthreads();
+            b_spmv_Q(P, V.Qv, V.dx, V.Qdx);
+            b_spmv_A(P, V.Av, V.dx, V.Adx);
+            __syncthreads();
+            if (proximal) { FOR_N(i) V.Qdx[i] = V.Qdx[i] + sigma * V.dx[i]; }
+            FOR_M(i) { if (V.act[i]) V.dy[i] = V.dy[i] + V.Adx[i] / V.mu[i]; }
+            __syncthreads();
+            b_spmv_At(P, V.Av, V.dy, V.Atdy);
+            __syncthreads();
+            tau = b_linesearch(P, V);
+            FOR_N(i) { V.x[i] = V.x[i] + tau * V.dx[i]; V.Qx[i] = V.Qx[i] + tau * V.Qdx[i]; V.Aty[i] = V.Aty[i] + tau * V.Atdy[i]; }
+            FOR_M(i) { V.y[i] = V.y[i] + tau * V.dy[i]; V.Ax[i] = V.Ax[i] + tau * V.Adx[i]; }
+            __syncthreads();
+        }
+    }
+    if (status == QPDO_UNSOLVED) status = QPDO_MAX_ITER_REACHED;
+    // ---- store_solution (termination.c:82-92) + compute_objective (iteration.c:185-221)
+    __syncthreads();
+    double ob[1] = {0.0};
+    FOR_N(i) { const double t = proximal ? 0.5 * (V.Qx[i] - V.x[i] * sigma) + V.q[i] : 0.5 * V.Qx[i] + V.q[i]; ob[0] += t * V.x[i]; }
+    block_sum<1>(ob, red);
+    double objective = ob[0];
+    if (scaled) objective = objective * cinv;
+    objective = objective + (io.c ? io.c[b] : 0.0);
+    if (io.x) { FOR_N(i) io.x[(size_t)b * n + i] = scaled ? V.x[i] * V.D[i] : V.x[i]; }
+    if (io.y) { FOR_M(i) { double v = V.y[i]; if (scaled) { v = v * cinv; v = v * V.E[i]; } io.y[(size_t)b * m + i] = v; } }
+    if (io.active) { FOR_M(i) io.active[(size_t)b * m + i] = V.act[i]; }
+    if (io.summary && tid == 0) {
+        qpdo_batch_summary s;
+        s.status_val = status; s.iterations = iter; s.oterations = oter; s.n_active = n_active;
+        s.objective = objective; s.res_prim_norm = rpn; s.res_dual_norm = rdn;
+        io.summary[b] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------- kernel
+__global__ void __launch_bounds__(BNT, 2) k_batch_solve(const BatchPlan P, const BatchIO io)
+{
+    extern __shared__ double sm[];
+    __shared__ int s_b;
+    const int n = P.n, m = P.m;
+    BVec V;
+    double *p = sm;
+    V.Av = p; p += P.nnzA; V.Qv = p; p += P.nnzQ;
+#define TAKE(ptr, len) ptr = p; p += (len);
+    TAKE(V.q, n) TAKE(V.x, n) TAKE(V.xbar, n) TAKE(V.Qx, n) TAKE(V.Aty, n) TAKE(V.dx, n) TAKE(V.Qdx, n) TAKE(V.Atdy, n)
+    TAKE(V.df, n) TAKE(V.rdi, n) TAKE(V.tn, n) TAKE(V.D, n)
+    TAKE(V.l, m) TAKE(V.u, m) TAKE(V.y, m) TAKE(V.ybar, m) TAKE(V.Ax, m) TAKE(V.dy, m) TAKE(V.Adx, m) TAKE(V.w, m)
+    TAKE(V.rp, m) TAKE(V.rpo, m) TAKE(V.rpi, m) TAKE(V.mu, m) TAKE(V.smu, m) TAKE(V.om, m) TAKE(V.E, m) TAKE(V.tm, m)
+#undef TAKE
+    V.K = p; p += P.karea;
+    V.red = p; p += BNW * 8;
+    V.act = (unsigned char *)p; V.acto = V.act + m;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_b = atomicAdd(io.next, 1);
+        __syncthreads();
+        const int b = s_b;
+        if (b >= io.count) break;
+        b_solve_instance(P, io, V, b);
+    }
+}
+
+// =============================================================================== host side
+struct qpdo_batch {
+    int n = 0, m = 0, nnzA = 0, nnzQ = 0, capacity = 0, device = 0, lnz = 0;
+    BatchPlan P;
+    size_t smem = 0;
+    int ctas = 0;
+    cudaStream_t st = nullptr;
+    std::vector<void *> allocs;
+    // staging for the host-buffer entry point
+    double *dQx = nullptr, *dAx = nullptr, *dq = nullptr, *dl = nullptr, *du = nullptr, *dc = nullptr, *dx0 = nullptr, *dy0 = nullptr;
+    double *dx = nullptr, *dy = nullptr;
+    qpdo_batch_summary *dsum = nullptr;
+    unsigned char *dact = nullptr;
+    int *next = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+
+template <class T> static int b_alloc(qpdo_batch *b, T **p, size_t count)
+{
+    void *v = nullptr;
+    cudaError_t e = cudaMalloc(&v, sizeof(T) * (count ? count : 1));
+    if (e != cudaSuccess) { qpdo_set_error("cudaMalloc(%zu): %s", sizeof(T) * count, cudaGetErrorString(e)); return -1; }
+    b->allocs.push_back(v);
+    *p = (T *)v;
+    return 0;
+}
+template <class T> static int b_upload(qpdo_batch *b, const T **p, const std::vector<T> &h)
+{
+    T *d = nullptr;
+    if (b_alloc(b, &d, h.size())) return -1;
+    if (!h.empty()) CUDA_OK(cudaMemcpy(d, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice));
+    *p = d;
+    return 0;
+}
+
+extern "C" void qpdo_batch_destroy(qpdo_batch *b)
+{
+    if (!b) return;
+    cudaSetDevice(b->device);
+    if (b->st) cudaStreamSynchronize(b->st);
+    for (void *p : b->allocs) cudaFree(p);
+    if (b->e0) cudaEventDestroy(b->e0);
+    if (b->e1) cudaEventDestroy(b->e1);
+    if (b->st) cudaStreamDestroy(b->st);
+    delete b;
+}
+
+extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, const int *Qi, const int *Ap, const int *Ai,
+                                 int capacity, const QPDOSettings *s, int device)
+{
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { qpdo_set_error("no CUDA device available: qpdo_b200 has no CPU fallback"); return -2; }
+    if (n <= 0 || m < 0 || capacity <= 0 || !s) { qpdo_set_error("qpdo_batch_create: bad arguments"); return -3; }
+    // validate_settings (reference src/validate.c:34-170)
+    if (!(s->max_iter > 0 && s->inner_max_iter > 0 && s->eps_abs > 0 && s->eps_abs_in > 0 && s->eps_prim_inf >= 0 && s->eps_dual_inf >= 0 &&
+          s->rho > 0 && s->rho < 1 && s->theta > 0 && s->theta <= 1 && s->delta > 0 && s->delta < 1 && s->mu_min > 0 &&
+          (s->proximal == 0 || s->proximal == 1) && s->sigma_init > 0 && s->sigma_upd > 0 && s->sigma_upd <= 1 &&
+          !(s->sigma_min > s->sigma_init) && s->scaling >= 0 && s->reset_newton_iter >= 0)) {
+        qpdo_set_error("qpdo_batch_create: settings validation returned failure");
+        return -3;
+    }
+    if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) device = 0; }
+    CUDA_OK(cudaSetDevice(device));
+    char err[256];
+    qpdo_symbolic *S = qpdo_symbolic_analyze(n, m, Qp, Qi, Ap, Ai, 1, err);
+    if (!S) { qpdo_set_error("symbolic analysis failed: %s", err); return -1; }
+    qpdo_batch *b = new qpdo_batch();
+    b->n = n; b->m = m; b->nnzQ = Qp[n]; b->nnzA = Ap[n]; b->capacity = capacity; b->device = device;
+    int rc = -1;
+    do {
+        const int nnzA = b->nnzA, nnzQ = b->nnzQ;
+        // CSR of A, full symmetric CSR of Q (same construction as qpdo_dev_create)
+        std::vector<int> Rp(m + 1, 0), Rj(nnzA), Rsrc(nnzA);
+        for (int k = 0; k < nnzA; k++) Rp[Ai[k] + 1]++;
+        for (int i = 0; i < m; i++) Rp[i + 1] += Rp[i];
+        { std::vector<int> nx(Rp.begin(), Rp.end() - 1);
+          for (int j = 0; j < n; j++) for (int k = Ap[j]; k < Ap[j + 1]; k++) { int t = nx[Ai[k]]++; Rj[t] = j; Rsrc[t] = k; } }
+        std::vector<int> Fp(n + 1, 0), Fdiag(n, 0);
+        for (int j = 0; j < n; j++) for (int k = Qp[j]; k < Qp[j + 1]; k++) { int i = Qi[k]; Fp[i + 1]++; Fdiag[i]++; if (i != j) Fp[j + 1]++; }
+        for (int i = 0; i < n; i++) Fp[i + 1] += Fp[i];
+        std::vector<int> Fj(Fp[n]), Fsrc(Fp[n]);
+        { std::vector<int> nx(Fp.begin(), Fp.end() - 1);
+          for (int j = 0; j < n; j++) for (int k = Qp[j]; k < Qp[j + 1]; k++) { int i = Qi[k]; int t = nx[i]++; Fj[t] = j; Fsrc[t] = k; }
+          for (int j = 0; j < n; j++) for (int k = Qp[j]; k < Qp[j + 1]; k++) { int i = Qi[k]; if (i != j) { int t = nx[j]++; Fj[t] = i; Fsrc[t] = k; } } }
+        // pattern of L from the supernodes: column j of supernode [f, l]: rows j+1..l, then the supernode's rows
+        std::vector<int> Lcp(n + 1, 0), Lri;
+        for (int sn = 0; sn < S->nsuper; sn++) {
+            const int f = S->sn_start[sn], l = S->sn_start[sn + 1] - 1;
+            for (int j = f; j <= l; j++) {
+                for (int i = j + 1; i <= l; i++) Lri.push_back(i);
+                for (int64_t t = S->sn_rowptr[sn]; t < S->sn_rowptr[sn + 1]; t++) Lri.push_back(S->rows[t]);
+                Lcp[j + 1] = (int)Lri.size();
+            }
+        }
+        b->lnz = (int)Lri.size() + n;
+        std::vector<int> Lrp(n + 1, 0), Lci(Lri.size());
+        for (int r : Lri) Lrp[r + 1]++;
+        for (int i = 0; i < n; i++) Lrp[i + 1] += Lrp[i];
+        { std::vector<int> nx(Lrp.begin(), Lrp.end() - 1);
+          for (int j = 0; j < n; j++) for (int t = Lcp[j]; t < Lcp[j + 1]; t++) Lci[nx[Lri[t]]++] = j; }
+        // K entries -> packed positions
+        const int nnzK = (int)S->nnzK;
+        std::vector<int> Kpos(nnzK), Kq(S->Kq, S->Kq + nnzK), Ktp(nnzK + 1);
+        std::vector<unsigned char> Kdiag(nnzK);
+        for (int k = 0; k < n; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++) {
+            const int i = S->Ki[e];
+            Kpos[e] = k * n - ((k * (k - 1)) >> 1) - k + i;
+            Kdiag[e] = (i == k);
+        }
+        for (int e = 0; e <= nnzK; e++) Ktp[e] = (int)S->Ktp[e];
+        std::vector<int> Kt_row(S->Kt_row, S->Kt_row + S->ntriple), Kt_a1(S->Kt_a1, S->Kt_a1 + S->ntriple), Kt_a2(S->Kt_a2, S->Kt_a2 + S->ntriple);
+        std::vector<int> perm(S->perm, S->perm + n), vQp(Qp, Qp + n + 1), vQi(Qi, Qi + nnzQ), vAp(Ap, Ap + n + 1), vAi(Ai, Ai + nnzA);
+        BatchPlan &P = b->P;
+        memset(&P, 0, sizeof P);
+        P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK; P.nKpack = n * (n + 1) / 2;
+        int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
+        P.P2 = P2;
+        P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
+        if (b_upload(b, &P.Ap, vAp) || b_upload(b, &P.Ai, vAi) || b_upload(b, &P.Rp, Rp) || b_upload(b, &P.Rj, Rj) || b_upload(b, &P.Rsrc, Rsrc) ||
+            b_upload(b, &P.Qp, vQp) || b_upload(b, &P.Qi, vQi) || b_upload(b, &P.Fp, Fp) || b_upload(b, &P.Fj, Fj) || b_upload(b, &P.Fsrc, Fsrc) ||
+            b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kpos, Kpos) || b_upload(b, &P.Kq, Kq) ||
+            b_upload(b, &P.Ktp, Ktp) || b_upload(b, &P.Kt_row, Kt_row) || b_upload(b, &P.Kt_a1, Kt_a1) || b_upload(b, &P.Kt_a2, Kt_a2) ||
+            b_upload(b, &P.Kdiag, Kdiag) || b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
+            break;
+        P.max_iter = (int)s->max_iter; P.inner_max_iter = (int)s->inner_max_iter; P.proximal = (int)s->proximal; P.scaling = (int)s->scaling;
+        P.reset_newton_iter = (int)s->reset_newton_iter;
+        P.eps_abs = s->eps_abs; P.eps_abs_in = s->eps_abs_in; P.eps_prim_inf = s->eps_prim_inf; P.eps_dual_inf = s->eps_dual_inf;
+        P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
+        P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
+        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8) + 2 * (size_t)m + 16;
+        if (b->smem > 227 * 1024) {
+            qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
+            break;
+        }
+        if (cudaFuncSetAttribute(k_batch_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem) != cudaSuccess) { qpdo_set_error("cudaFuncSetAttribute failed"); break; }
+        int per_sm = 0, sms = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_solve, BNT, b->smem);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        b->ctas = std::max(1, per_sm) * std::max(1, sms);
+        if (cudaStreamCreateWithFlags(&b->st, cudaStreamNonBlocking) != cudaSuccess) { qpdo_set_error("cudaStreamCreate failed"); break; }
+        cudaEventCreate(&b->e0); cudaEventCreate(&b->e1);
+        const size_t cap = (size_t)capacity;
+        if (b_alloc(b, &b->dQx, cap * nnzQ) || b_alloc(b, &b->dAx, cap * nnzA) || b_alloc(b, &b->dq, cap * n) || b_alloc(b, &b->dl, cap * m) ||
+            b_alloc(b, &b->du, cap * m) || b_alloc(b, &b->dc, cap) || b_alloc(b, &b->dx0, cap * n) || b_alloc(b, &b->dy0, cap * m) ||
+            b_alloc(b, &b->dx, cap * n) || b_alloc(b, &b->dy, cap * m) || b_alloc(b, &b->dsum, cap) || b_alloc(b, &b->dact, cap * m) ||
+            b_alloc(b, &b->next, 1))
+            break;
+        rc = 0;
+    } while (0);
+    qpdo_symbolic_free(S);
+    if (rc) { qpdo_batch_destroy(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *dQx, const double *dAx, const double *dq,
+                                       const double *dl, const double *du, const double *dc, const double *dx0, const double *dy0,
+                                       double *dx, double *dy, qpdo_batch_summary *dsummary, unsigned char *dactive, int sync,
+                                       float *kernel_ms)
+{
+    if (!b || count < 0 || !dQx || !dAx || !dq || !dl || !du) { qpdo_set_error("qpdo_batch_solve_device: bad arguments"); return -3; }
+    if (count == 0) return 0;
+    CUDA_OK(cudaSetDevice(b->device));
+    BatchIO io;
+    io.Qx = dQx; io.Ax = dAx; io.q = dq; io.l = dl; io.u = du; io.c = dc; io.x0 = dx0; io.y0 = dy0;
+    io.x = dx; io.y = dy; io.summary = dsummary; io.active = dactive; io.count = count; io.next = b->next;
+    CUDA_OK(cudaMemsetAsync(b->next, 0, sizeof(int), b->st));
+    if (kernel_ms) CUDA_OK(cudaEventRecord(b->e0, b->st));
+    const int grid = std::min(count, b->ctas);
+    k_batch_solve<<<grid, BNT, b->smem, b->st>>>(b->P, io);
+    CUDA_OK(cudaGetLastError());
+    if (kernel_ms) CUDA_OK(cudaEventRecord(b->e1, b->st));
+    if (sync || kernel_ms) {
+        CUDA_OK(cudaStreamSynchronize(b->st));
+        if (kernel_ms) CUDA_OK(cudaEventElapsedTime(kernel_ms, b->e0, b->e1));
+    }
+    return 0;
+}
+
+extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, const double *Ax, const double *q, const double *l,
+                                const double *u, const double *c, const double *x0, const double *y0, double *x, double *y,
+                                qpdo_batch_summary *summary, unsigned char *active_set)
+{
+    if (!b || count < 0 || count > b->capacity || !Qx || !Ax || !q || !l || !u) { qpdo_set_error("qpdo_batch_solve: bad arguments (count > capacity?)"); return -3; }
+    if (count == 0) return 0;
+    CUDA_OK(cudaSetDevice(b->device));
+    const size_t cn = (size_t)count, n = b->n, m = b->m, D = sizeof(double);
+    CUDA_OK(cudaMemcpyAsync(b->dQx, Qx, D * cn * b->nnzQ, cudaMemcpyHostToDevice, b->st));
+    CUDA_OK(cudaMemcpyAsync(b->dAx, Ax, D * cn * b->nnzA, cudaMemcpyHostToDevice, b->st));
+    CUDA_OK(cudaMemcpyAsync(b->dq, q, D * cn * n, cudaMemcpyHostToDevice, b->st));
+    if (m) CUDA_OK(cudaMemcpyAsync(b->dl, l, D * cn * m, cudaMemcpyHostToDevice, b->st));
+    if (m) CUDA_OK(cudaMemcpyAsync(b->du, u, D * cn * m, cudaMemcpyHostToDevice, b->st));
+    if (c) CUDA_OK(cudaMemcpyAsync(b->dc, c, D * cn, cudaMemcpyHostToDevice, b->st));
+    if (x0) CUDA_OK(cudaMemcpyAsync(b->dx0, x0, D * cn * n, cudaMemcpyHostToDevice, b->st));
+    if (y0 && m) CUDA_OK(cudaMemcpyAsync(b->dy0, y0, D * cn * m, cudaMemcpyHostToDevice, b->st));
+    if (qpdo_batch_solve_device(b, count, b->dQx, b->dAx, b->dq, b->dl, b->du, c ? b->dc : nullptr, x0 ? b->dx0 : nullptr,
+                                (y0 && m) ? b->dy0 : nullptr, b->dx, b->dy, b->dsum, b->dact, 0, nullptr))
+        return -1;
+    if (x) CUDA_OK(cudaMemcpyAsync(x, b->dx, D * cn * n, cudaMemcpyDeviceToHost, b->st));
+    if (y && m) CUDA_OK(cudaMemcpyAsync(y, b->dy, D * cn * m, cudaMemcpyDeviceToHost, b->st));
+    if (summary) CUDA_OK(cudaMemcpyAsync(summary, b->dsum, sizeof(qpdo_batch_summary) * cn, cudaMemcpyDeviceToHost, b->st));
+    if (active_set && m) CUDA_OK(cudaMemcpyAsync(active_set, b->dact, cn * m, cudaMemcpyDeviceToHost, b->st));
+    cudaError_t e = cudaStreamSynchronize(b->st);
+    if (e != cudaSuccess) { qpdo_set_error("batch kernel failed: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+extern "C" int qpdo_batch_info(const qpdo_batch *b, int *smem_bytes, int *ctas, int *lnz, int *threads)
+{
+    if (!b) return -3;
+    if (smem_bytes) *smem_bytes = (int)b->smem;
+    if (ctas) *ctas = b->ctas;
+    if (lnz) *lnz = b->lnz;
+    if (threads) *threads = BNT;
+    return 0;
+}
+
+// ---- arrays of the reference's own QPDOData (include/types.h:81-90) that share one pattern
+static int data_to_csc(const cholmod_sparse *S, int lower, std::vector<int> &p, std::vector<int> &i, std::vector<double> &x)
+{
+    const bool il = (S->itype == QPDO_CHOLMOD_LONG);
+    auto idx = [&](const void *a, size_t k) { return il ? (long)((const long *)a)[k] : (long)((const int *)a)[k]; };
+    const size_t ncol = S->ncol;
+    p.assign(ncol + 1, 0); i.clear(); x.clear();
+    const double *Sx = (const double *)S->x;
+    for (size_t j = 0; j < ncol; j++) {
+        long b = idx(S->p, j), e = S->packed ? idx(S->p, j + 1) : b + idx(S->nz, j);
+        long prev = -1;
+        for (long k = b; k < e; k++) {
+            long r = idx(S->i, (size_t)k);
+            if (lower && r < (long)j) continue;
+            if (r <= prev) return -1;              // unsorted or duplicate: not supported by the batch entry
+            prev = r;
+            i.push_back((int)r); x.push_back(Sx[k]);
+        }
+        p[j + 1] = (int)i.size();
+    }
+    return 0;
+}
+
+extern "C" int qpdo_batch_solve_data(const QPDOData *const *data, int count, const QPDOSettings *settings, double *const *x,
+                                     double *const *y, qpdo_batch_summary *summary, int device)
+{
+    if (!data || count <= 0 || !settings) { qpdo_set_error("qpdo_batch_solve_data: bad arguments"); return -3; }
+    const int n = (int)data[0]->n, m = (int)data[0]->m;
+    std::vector<int> Qp, Qi, Ap, Ai, p2, i2;
+    std::vector<double> v;
+    std::vector<double> Qx, Ax, q((size_t)count * n), l((size_t)count * m), u((size_t)count * m), c(count);
+    for (int k = 0; k < count; k++) {
+        const QPDOData *d = data[k];
+        if ((int)d->n != n || (int)d->m != m || d->Q->stype > 0) { qpdo_set_error("qpdo_batch_solve_data: instance %d has another shape (or upper-stored Q)", k); return -4; }
+        for (size_t j = 0; j < (size_t)m; j++) if (d->l[j] > d->u[j]) { qpdo_set_error("instance %d: lower bound %zu above upper bound", k, j); return -3; }
+        if (data_to_csc(d->Q, 1, p2, i2, v)) { qpdo_set_error("instance %d: Q must have sorted, duplicate-free columns", k); return -4; }
+        if (k == 0) { Qp = p2; Qi = i2; Qx.reserve((size_t)count * v.size()); }
+        else if (p2 != Qp || i2 != Qi) { qpdo_set_error("qpdo_batch_solve_data: instance %d does not share the pattern of Q", k); return -4; }
+        Qx.insert(Qx.end(), v.begin(), v.end());
+        if (data_to_csc(d->A, 0, p2, i2, v)) { qpdo_set_error("instance %d: A must have sorted, duplicate-free columns", k); return -4; }
+        if (k == 0) { Ap = p2; Ai = i2; Ax.reserve((size_t)count * v.size()); }
+        else if (p2 != Ap || i2 != Ai) { qpdo_set_error("qpdo_batch_solve_data: instance %d does not share the pattern of A", k); return -4; }
+        Ax.insert(Ax.end(), v.begin(), v.end());
+        memcpy(&q[(size_t)k * n], d->q, sizeof(double) * n);
+        if (m) { memcpy(&l[(size_t)k * m], d->l, sizeof(double) * m); memcpy(&u[(size_t)k * m], d->u, sizeof(double) * m); }
+        c[k] = d->c;
+    }
+    qpdo_batch *b = nullptr;
+    int rc = qpdo_batch_create(&b, n, m, Qp.data(), Qi.data(), Ap.data(), Ai.data(), count, settings, device);
+    if (rc) return rc;
+    std::vector<double> xs((size_t)count * n), ys((size_t)count * m);
+    rc = qpdo_batch_solve(b, count, Qx.data(), Ax.data(), q.data(), l.data(), u.data(), c.data(), nullptr, nullptr, xs.data(), ys.data(), summary, nullptr);
+    if (!rc) for (int k = 0; k < count; k++) {
+        if (x && x[k]) memcpy(x[k], &xs[(size_t)k * n], sizeof(double) * n);
+        if (y && y[k] && m) memcpy(y[k], &ys[(size_t)k * m], sizeof(double) * m);
+    }
+    qpdo_batch_destroy(b);
+    return rc;
+}
