@@ -144,3 +144,36 @@ def ref_library(nosuper=False):
     """the unmodified reference as a qpdo.h library (driven through qpdo_b200.capi.Solver)."""
     from qpdo_b200 import capi
     return capi.load_library(REF_NOSUPER if nosuper else REF)
+
+
+REF_BATCH = os.path.join(HERE, "libref_batch.so")
+REF_SUMMARY = np.dtype([("status_val", np.int32), ("iterations", np.int32), ("oterations", np.int32),
+                        ("n_active", np.int32), ("objective", np.float64), ("res_prim_norm", np.float64),
+                        ("res_dual_norm", np.float64)])
+
+
+def ref_batch_loop(n, m, Qp, Qi, Ap, Ai, Qx, Ax, q, l, u, threads=1, max_iter=0, nosuper=False, want_xy=False):
+    """The reference user's loop (qpdo_setup / qpdo_solve / qpdo_cleanup per problem, src/qpdo.c:49,304,591)
+    over a packed batch, on `threads` host threads, with the unmodified reference library
+    (oracle/ref_batch.c).  Returns (wall seconds, summaries[, x, y])."""
+    if not os.path.exists(REF_BATCH):
+        build(ref=False)
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")       # one workspace per thread; BLAS stays serial
+    L = C.CDLL(REF_BATCH)
+    L.ref_batch_run.restype = C.c_double
+    L.ref_batch_run.argtypes = [C.c_char_p, C.c_long, C.c_long, C.c_long, _pl, _pl, _pl, _pl, _pd, _pd, _pd, _pd, _pd,
+                                C.c_long, C.c_int, _pd, _pd, C.c_void_p]
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    g = lambda a: np.ascontiguousarray(a, dtype=np.int64)
+    Qp, Qi, Ap, Ai = map(g, (Qp, Qi, Ap, Ai))
+    Qx, Ax, q, l, u = map(f, (Qx, Ax, q, l, u))
+    count = q.shape[0]
+    summ = np.zeros(count, dtype=REF_SUMMARY)
+    x = np.zeros((count, n)) if want_xy else None
+    y = np.zeros((count, m)) if want_xy else None
+    path = REF_NOSUPER if nosuper else REF
+    secs = L.ref_batch_run(path.encode(), count, n, m, _p(Qp, _pl), _p(Qi, _pl), _p(Ap, _pl), _p(Ai, _pl), _p(Qx), _p(Ax),
+                           _p(q), _p(l), _p(u), max_iter, threads, _p(x), _p(y), summ.ctypes.data)
+    if secs < 0:
+        raise RuntimeError("ref_batch_run failed (%g)" % secs)
+    return (secs, summ, x, y) if want_xy else (secs, summ)
