@@ -18,10 +18,11 @@
 #include "dev_internal.h"
 #include "qpdo_batch.h"
 #include <algorithm>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
-#define BNT 256                 // threads per CTA
+#define BNT 128                 // threads per CTA
 #define BNW (BNT / 32)
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
@@ -38,6 +39,12 @@ struct BatchPlan {
     const unsigned char *Kdiag;
     const int *Lcp, *Lri;                    // L column patterns (rows strictly below the diagonal)
     const int *Lrp, *Lci;                    // L row patterns (columns strictly left of the diagonal)
+    // supernodal register path (mode 1): every front fits one warp (N + 1 <= 32 lanes)
+    int mode, nsuper;
+    const int *sn_f, *sn_nc, *sn_nr;         // first column, pivot columns, rows below the pivot block
+    const int *sn_base;                      // offset of the packed trapezoid of each supernode in the L area
+    const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
+    const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
     // settings (reference include/types.h:96-116)
     int max_iter, inner_max_iter, proximal, scaling, reset_newton_iter;
     double eps_abs, eps_abs_in, eps_prim_inf, eps_dual_inf, rho, theta, delta, mu_min, sigma_init, sigma_upd, sigma_min;
@@ -196,6 +203,94 @@ __device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, 
         }
     }
     __syncthreads();
+}
+
+// ---- supernodal register path -------------------------------------------------------------------
+// L is stored as one packed trapezoid per supernode: pivot column jj holds front rows jj..N-1
+// (diagonal = D, below = unit-L entries), at base + jj*N - jj(jj-1)/2 + (i - jj).  One warp owns a
+// whole front: lane i keeps row i of the front (pivot columns AND the columns of the update block,
+// which are gathered from / written back to the ancestors' trapezoids) in registers, lane N keeps the
+// right-hand side as an extra row.  The right-looking elimination then needs no shared memory and no
+// barrier: the pivot and the scaled column entries travel by warp shuffle.  Per entry the sequence
+// of fma's is the one b_factor_forward performs (ascending k, same operands), so both paths give
+// bit-identical factors and solves.
+#define SN_NMAX 31              // front order limit (N + 1 lanes)
+#define SN_NCMAX 24             // pivot columns per supernode (unrolled elimination steps)
+__device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + jj * N - ((jj * (jj - 1)) >> 1) - jj; }   // + front row i
+__device__ __noinline__ void b_factor_sn(const BatchPlan &P, double *L, double *xs)
+{
+    const int lane = threadIdx.x & 31;
+    for (int s = 0; s < P.nsuper; s++) {
+        const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
+        const int *rows = P.Srow + P.Sptr[s], *up = P.Upos + P.Uptr[s];
+        double a[SN_NMAX];
+#pragma unroll
+        for (int j = 0; j < SN_NMAX; j++) {
+            a[j] = 0.0;
+            if (j < nc) {
+                if (lane >= j && lane < N) a[j] = L[sn_col(base, j, N) + lane];
+                else if (lane == N) a[j] = xs[f + j];
+            } else if (j < N) {
+                if (lane >= j && lane < N) a[j] = L[up[(j - nc) * nr + lane - nc]];
+                else if (lane == N) a[j] = xs[rows[j - nc]];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < SN_NCMAX; k++) {
+            if (k < nc) {
+                const double dk = __shfl_sync(0xffffffffu, a[k], k);
+                const double ak = a[k];
+                const double lk = ak / dk;
+#pragma unroll
+                for (int j0 = k + 1; j0 < SN_NMAX; j0 += 4) {
+                    if (j0 < N) {
+#pragma unroll
+                        for (int j = j0; j < j0 + 4 && j < SN_NMAX; j++) {
+                            const double ljk = __shfl_sync(0xffffffffu, lk, j);
+                            a[j] = fma(-ak, ljk, a[j]);
+                        }
+                    }
+                }
+                if (lane > k) a[k] = lk;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < SN_NMAX; j++) {
+            if (j < nc) {
+                if (lane >= j && lane < N) L[sn_col(base, j, N) + lane] = a[j];
+                else if (lane == N) xs[f + j] = a[j];
+            } else if (j < N) {
+                if (lane >= j && lane < N) L[up[(j - nc) * nr + lane - nc]] = a[j];
+                else if (lane == N) xs[rows[j - nc]] = a[j];
+            }
+        }
+        __syncwarp();
+    }
+}
+// x = L^{-T} xs: lane c owns pivot column c of the front, lanes nc..N-1 carry the already final
+// entries of the rows below; same fma sequence per entry as b_backward (descending row order)
+__device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, double *xs)
+{
+    const int lane = threadIdx.x & 31;
+    for (int s = P.nsuper - 1; s >= 0; s--) {
+        const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
+        const int *rows = P.Srow + P.Sptr[s];
+        const int mycol = sn_col(base, lane, N);
+        double col[SN_NMAX];
+#pragma unroll
+        for (int i = 1; i < SN_NMAX; i++) col[i] = (i < N && lane < nc && lane < i) ? L[mycol + i] : 0.0;
+        double v = 0.0;
+        if (lane < nc) v = xs[f + lane]; else if (lane < N) v = xs[rows[lane - nc]];
+#pragma unroll
+        for (int i = SN_NMAX - 1; i >= 1; i--) {
+            if (i < N) {
+                const double xi = __shfl_sync(0xffffffffu, v, i);
+                if (lane < i && lane < nc) v = fma(-col[i], xi, v);
+            }
+        }
+        if (lane < nc) xs[f + lane] = v;
+        __syncwarp();
+    }
 }
 
 // ------------------------------------------------------------------------------- exact linesearch
@@ -619,8 +714,13 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             b_assemble(P, V.Av, V.Qv, V.om, sigma, V.K);            // ends with __syncthreads
             FOR_N(k) { const int o = P.perm[k]; V.tn[k] = -V.rdi[o] - V.Atdy[o]; }     // P * rhs (newton.c:43-45)
             __syncthreads();
-            b_factor_forward(P, V.K, V.tn);
-            b_backward(P, V.K, V.tn);
+            if (P.mode == 1) {
+                if (tid < 32) { b_factor_sn(P, V.K, V.tn); b_backward_sn(P, V.K, V.tn); }
+                __syncthreads();
+            } else {
+                b_factor_forward(P, V.K, V.tn);
+                b_backward(P, V.K, V.tn);
+            }
             FOR_N(k) V.dx[P.perm[k]] = V.tn[k];
             __syncthreads();
             b_spmv_Q(P, V.Qv, V.dx, V.Qdx);
@@ -658,7 +758,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
 }
 
 // ------------------------------------------------------------------------------- kernel
-__global__ void __launch_bounds__(BNT, 2) k_batch_solve(const BatchPlan P, const BatchIO io)
+__global__ void __launch_bounds__(BNT, 4) k_batch_solve(const BatchPlan P, const BatchIO io)
 {
     extern __shared__ double sm[];
     __shared__ int s_b;
@@ -687,7 +787,7 @@ __global__ void __launch_bounds__(BNT, 2) k_batch_solve(const BatchPlan P, const
 
 // =============================================================================== host side
 struct qpdo_batch {
-    int n = 0, m = 0, nnzA = 0, nnzQ = 0, capacity = 0, device = 0, lnz = 0;
+    int n = 0, m = 0, nnzA = 0, nnzQ = 0, capacity = 0, device = 0, lnz = 0, mode = 0;
     BatchPlan P;
     size_t smem = 0;
     int ctas = 0;
@@ -786,13 +886,60 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         for (int i = 0; i < n; i++) Lrp[i + 1] += Lrp[i];
         { std::vector<int> nx(Lrp.begin(), Lrp.end() - 1);
           for (int j = 0; j < n; j++) for (int t = Lcp[j]; t < Lcp[j + 1]; t++) Lci[nx[Lri[t]]++] = j; }
+        // supernodal register path (mode 1) when every front fits one warp; QPDO_BATCH_FACTOR=columns forces
+        // the column-by-column path (mode 0) for A/B tests
+        int mode = 1;
+        for (int sn = 0; sn < S->nsuper; sn++) {
+            const int nc = S->sn_start[sn + 1] - S->sn_start[sn];
+            if (nc > SN_NCMAX || nc + S->sn_nr[sn] > SN_NMAX) mode = 0;
+        }
+        { const char *ev = getenv("QPDO_BATCH_FACTOR"); if (ev && !strcmp(ev, "columns")) mode = 0; }
+        std::vector<int> sn_f(S->nsuper), sn_nc(S->nsuper), sn_nr(S->nsuper), sn_base(S->nsuper), Sptr(S->nsuper + 1, 0), Srow, Uptr(S->nsuper + 1, 0), Upos;
+        {
+            int off = 0;
+            for (int sn = 0; sn < S->nsuper; sn++) {
+                sn_f[sn] = S->sn_start[sn]; sn_nc[sn] = S->sn_start[sn + 1] - S->sn_start[sn]; sn_nr[sn] = S->sn_nr[sn];
+                sn_base[sn] = off;
+                const int N = sn_nc[sn] + sn_nr[sn];
+                off += sn_nc[sn] * N - sn_nc[sn] * (sn_nc[sn] - 1) / 2;
+                for (int64_t t = S->sn_rowptr[sn]; t < S->sn_rowptr[sn + 1]; t++) Srow.push_back(S->rows[t]);
+                Sptr[sn + 1] = (int)Srow.size();
+            }
+        }
+        // position of entry (row i, col k), i >= k (permuted indices) in the trapezoids; -1 if outside the pattern of L
+        auto trap_pos = [&](int i, int k) -> int {
+            const int sn = S->col2sn[k], f = sn_f[sn], nc = sn_nc[sn], N = nc + sn_nr[sn], jj = k - f;
+            int fr;
+            if (i < f + nc) fr = i - f;
+            else {
+                const int *rb = Srow.data() + Sptr[sn], *re = Srow.data() + Sptr[sn + 1];
+                const int *it = std::lower_bound(rb, re, i);
+                if (it == re || *it != i) return -1;
+                fr = nc + (int)(it - rb);
+            }
+            return sn_base[sn] + jj * N - jj * (jj - 1) / 2 - jj + fr;
+        };
+        bool pattern_ok = true;
+        for (int sn = 0; sn < S->nsuper; sn++) {
+            const int nr = sn_nr[sn];
+            const int *rows = Srow.data() + Sptr[sn];
+            for (int jb = 0; jb < nr; jb++) for (int ib = 0; ib < nr; ib++) {
+                int pos = 0;
+                if (ib >= jb) { pos = trap_pos(rows[ib], rows[jb]); if (pos < 0) { pattern_ok = false; pos = 0; } }
+                Upos.push_back(pos);
+            }
+            Uptr[sn + 1] = (int)Upos.size();
+        }
+        if (!pattern_ok) mode = 0;
         // K entries -> packed positions
         const int nnzK = (int)S->nnzK;
         std::vector<int> Kpos(nnzK), Kq(S->Kq, S->Kq + nnzK), Ktp(nnzK + 1);
         std::vector<unsigned char> Kdiag(nnzK);
+        for (int k = 0; k < n && mode == 1; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++)
+            if (trap_pos(S->Ki[e], k) < 0) mode = 0;
         for (int k = 0; k < n; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++) {
             const int i = S->Ki[e];
-            Kpos[e] = k * n - ((k * (k - 1)) >> 1) - k + i;
+            Kpos[e] = mode == 1 ? trap_pos(i, k) : k * n - ((k * (k - 1)) >> 1) - k + i;
             Kdiag[e] = (i == k);
         }
         for (int e = 0; e <= nnzK; e++) Ktp[e] = (int)S->Ktp[e];
@@ -800,7 +947,9 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         std::vector<int> perm(S->perm, S->perm + n), vQp(Qp, Qp + n + 1), vQi(Qi, Qi + nnzQ), vAp(Ap, Ap + n + 1), vAi(Ai, Ai + nnzA);
         BatchPlan &P = b->P;
         memset(&P, 0, sizeof P);
-        P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK; P.nKpack = n * (n + 1) / 2;
+        P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK;
+        P.nKpack = mode == 1 ? b->lnz : n * (n + 1) / 2;
+        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode;
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
@@ -808,6 +957,8 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             b_upload(b, &P.Qp, vQp) || b_upload(b, &P.Qi, vQi) || b_upload(b, &P.Fp, Fp) || b_upload(b, &P.Fj, Fj) || b_upload(b, &P.Fsrc, Fsrc) ||
             b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kpos, Kpos) || b_upload(b, &P.Kq, Kq) ||
             b_upload(b, &P.Ktp, Ktp) || b_upload(b, &P.Kt_row, Kt_row) || b_upload(b, &P.Kt_a1, Kt_a1) || b_upload(b, &P.Kt_a2, Kt_a2) ||
+            b_upload(b, &P.sn_f, sn_f) || b_upload(b, &P.sn_nc, sn_nc) || b_upload(b, &P.sn_nr, sn_nr) || b_upload(b, &P.sn_base, sn_base) ||
+            b_upload(b, &P.Sptr, Sptr) || b_upload(b, &P.Srow, Srow) || b_upload(b, &P.Uptr, Uptr) || b_upload(b, &P.Upos, Upos) ||
             b_upload(b, &P.Kdiag, Kdiag) || b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
             break;
         P.max_iter = (int)s->max_iter; P.inner_max_iter = (int)s->inner_max_iter; P.proximal = (int)s->proximal; P.scaling = (int)s->scaling;
