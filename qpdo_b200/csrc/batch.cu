@@ -45,6 +45,8 @@ struct BatchPlan {
     const int *sn_base;                      // offset of the packed trapezoid of each supernode in the L area
     const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
     const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
+    const int *Eptr, *Emap;                  // owned-entry enumeration of each front: i | j << 8, column major, j >= 1, i = j..N
+    int max_front;
     // settings (reference include/types.h:96-116)
     int max_iter, inner_max_iter, proximal, scaling, reset_newton_iter;
     double eps_abs, eps_abs_in, eps_prim_inf, eps_dual_inf, rho, theta, delta, mu_min, sigma_init, sigma_upd, sigma_min;
@@ -205,66 +207,60 @@ __device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, 
     __syncthreads();
 }
 
-// ---- supernodal register path -------------------------------------------------------------------
+// ---- supernodal front path (mode 1) -------------------------------------------------------------
 // L is stored as one packed trapezoid per supernode: pivot column jj holds front rows jj..N-1
-// (diagonal = D, below = unit-L entries), at base + jj*N - jj(jj-1)/2 + (i - jj).  One warp owns a
-// whole front: lane i keeps row i of the front (pivot columns AND the columns of the update block,
-// which are gathered from / written back to the ancestors' trapezoids) in registers, lane N keeps the
-// right-hand side as an extra row.  The right-looking elimination then needs no shared memory and no
-// barrier: the pivot and the scaled column entries travel by warp shuffle.  Per entry the sequence
-// of fma's is the one b_factor_forward performs (ascending k, same operands), so both paths give
-// bit-identical factors and solves.
-#define SN_NMAX 31              // front order limit (N + 1 lanes)
-#define SN_NCMAX 24             // pivot columns per supernode (unrolled elimination steps)
+// (diagonal = D, below = unit-L entries), at base + jj*N - jj(jj-1)/2 + (i - jj).  The CTA eliminates
+// one dense front at a time: every thread OWNS up to SN_EPT entries (i, j) of the front's lower
+// triangle for the whole supernode -- pivot columns, the columns of the update block (which live in
+// the ancestors' trapezoids) and the right-hand side as an extra row i = N -- with their shared-memory
+// addresses in registers.  Step k: the rows below the pivot scale column k (u = a_ik, l = u / d_k) into
+// the ucol / lcol buffers, barrier, every owner applies a_ij = fma(-u_i, l_j, a_ij), barrier.  No index
+// loads and no address arithmetic on the critical path.  Per entry the sequence of fma's is the one
+// b_factor_forward performs (ascending k, same operands): both paths give bit-identical results.
+#define SN_NMAX 31              // b_backward_sn: front order limit (one lane per front row)
+#define SN_EPT 8                // owned entries per thread: fronts up to (N - 1)(N + 2) / 2 <= BNT * SN_EPT
 __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + jj * N - ((jj * (jj - 1)) >> 1) - jj; }   // + front row i
-__device__ __noinline__ void b_factor_sn(const BatchPlan &P, double *L, double *xs)
+__device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
-    const int lane = threadIdx.x & 31;
+    const int tid = threadIdx.x;
     for (int s = 0; s < P.nsuper; s++) {
         const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
-        const int *rows = P.Srow + P.Sptr[s], *up = P.Upos + P.Uptr[s];
-        double a[SN_NMAX];
+        const int *rows = P.Srow + P.Sptr[s], *up = P.Upos + P.Uptr[s], *emap = P.Emap + P.Eptr[s];
+        const int ne = P.Eptr[s + 1] - P.Eptr[s], ept = (ne + BNT - 1) / BNT;
+        double *lcol = ucol + N + 1;
+        int eij[SN_EPT];            // i | j << 8;  j == 0 never updates
+        double *ea[SN_EPT];
 #pragma unroll
-        for (int j = 0; j < SN_NMAX; j++) {
-            a[j] = 0.0;
-            if (j < nc) {
-                if (lane >= j && lane < N) a[j] = L[sn_col(base, j, N) + lane];
-                else if (lane == N) a[j] = xs[f + j];
-            } else if (j < N) {
-                if (lane >= j && lane < N) a[j] = L[up[(j - nc) * nr + lane - nc]];
-                else if (lane == N) a[j] = xs[rows[j - nc]];
+        for (int e = 0; e < SN_EPT; e++) {
+            eij[e] = 0; ea[e] = L;
+            const int idx = tid + e * BNT;
+            if (e < ept && idx < ne) {
+                const int code = emap[idx], i = code & 255, j = code >> 8;
+                eij[e] = code;
+                if (i == N) ea[e] = xs + (j < nc ? f + j : rows[j - nc]);
+                else if (j < nc) ea[e] = L + sn_col(base, j, N) + i;
+                else ea[e] = L + up[(j - nc) * nr + (i - nc)];
             }
         }
+        for (int k = 0; k < nc; k++) {
+            const int pc = sn_col(base, k, N);
+            if (tid < N - k) {                                  // rows k+1 .. N (N = right-hand side)
+                const int i = k + 1 + tid;
+                double *pa = (i < N) ? L + pc + i : xs + f + k;
+                const double u = *pa, dk = L[pc + k];
+                const double l = u / dk;
+                ucol[i] = u; lcol[i] = l; *pa = l;
+            }
+            __syncthreads();
 #pragma unroll
-        for (int k = 0; k < SN_NCMAX; k++) {
-            if (k < nc) {
-                const double dk = __shfl_sync(0xffffffffu, a[k], k);
-                const double ak = a[k];
-                const double lk = ak / dk;
-#pragma unroll
-                for (int j0 = k + 1; j0 < SN_NMAX; j0 += 4) {
-                    if (j0 < N) {
-#pragma unroll
-                        for (int j = j0; j < j0 + 4 && j < SN_NMAX; j++) {
-                            const double ljk = __shfl_sync(0xffffffffu, lk, j);
-                            a[j] = fma(-ak, ljk, a[j]);
-                        }
-                    }
+            for (int e = 0; e < SN_EPT; e++) {
+                if (e < ept) {
+                    const int i = eij[e] & 255, j = eij[e] >> 8;
+                    if (j > k) *ea[e] = fma(-ucol[i], lcol[j], *ea[e]);
                 }
-                if (lane > k) a[k] = lk;
             }
+            __syncthreads();
         }
-#pragma unroll
-        for (int j = 0; j < SN_NMAX; j++) {
-            if (j < nc) {
-                if (lane >= j && lane < N) L[sn_col(base, j, N) + lane] = a[j];
-                else if (lane == N) xs[f + j] = a[j];
-            } else if (j < N) {
-                if (lane >= j && lane < N) L[up[(j - nc) * nr + lane - nc]] = a[j];
-                else if (lane == N) xs[rows[j - nc]] = a[j];
-            }
-        }
-        __syncwarp();
     }
 }
 // x = L^{-T} xs: lane c owns pivot column c of the front, lanes nc..N-1 carry the already final
@@ -293,6 +289,22 @@ __device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, 
     }
 }
 
+// generic variant (fronts wider than a warp): one warp, column-parallel scatter per front row
+__device__ __noinline__ void b_backward_fronts(const BatchPlan &P, const double *L, double *xs)
+{
+    const int lane = threadIdx.x & 31;
+    for (int s = P.nsuper - 1; s >= 0; s--) {
+        const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
+        const int *rows = P.Srow + P.Sptr[s];
+        for (int i = N - 1; i >= 1; i--) {
+            const double xi = i >= nc ? xs[rows[i - nc]] : xs[f + i];
+            const int cend = i < nc ? i : nc;
+            for (int c = lane; c < cend; c += 32) xs[f + c] = fma(-L[sn_col(base, c, N) + i], xi, xs[f + c]);
+            __syncwarp();
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------- exact linesearch
 // reference src/linesearch.c:8-158; the CTA-wide version of k_ls_small (linesearch.cu): breakpoints
 // t_i = alpha_i / delta_i, keep t_i > 0, bitonic sort of (IEEE bits, index) in shared memory, prefix
@@ -300,7 +312,7 @@ __device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, 
 struct BVec {       // shared-memory vectors of one instance
     double *Av, *Qv, *q, *x, *xbar, *Qx, *Aty, *dx, *Qdx, *Atdy, *df, *rdi, *tn, *D;
     double *l, *u, *y, *ybar, *Ax, *dy, *Adx, *w, *rp, *rpo, *rpi, *mu, *smu, *om, *E, *tm;
-    double *K, *red;
+    double *K, *red, *ucol;
     unsigned char *act, *acto;
 };
 __device__ __forceinline__ void b_ls_contrib(const double *delta, const double *alpha, int iz, double &da, double &db)
@@ -715,7 +727,8 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             FOR_N(k) { const int o = P.perm[k]; V.tn[k] = -V.rdi[o] - V.Atdy[o]; }     // P * rhs (newton.c:43-45)
             __syncthreads();
             if (P.mode == 1) {
-                if (tid < 32) { b_factor_sn(P, V.K, V.tn); b_backward_sn(P, V.K, V.tn); }
+                b_factor_fronts(P, V.K, V.tn, V.ucol);
+                if (tid < 32) { if (P.max_front <= SN_NMAX) b_backward_sn(P, V.K, V.tn); else b_backward_fronts(P, V.K, V.tn); }
                 __syncthreads();
             } else {
                 b_factor_forward(P, V.K, V.tn);
@@ -774,6 +787,7 @@ __global__ void __launch_bounds__(BNT, 4) k_batch_solve(const BatchPlan P, const
 #undef TAKE
     V.K = p; p += P.karea;
     V.red = p; p += BNW * 8;
+    V.ucol = p; p += 2 * (P.max_front + 1);
     V.act = (unsigned char *)p; V.acto = V.act + m;
     for (;;) {
         __syncthreads();
@@ -888,10 +902,12 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
           for (int j = 0; j < n; j++) for (int t = Lcp[j]; t < Lcp[j + 1]; t++) Lci[nx[Lri[t]]++] = j; }
         // supernodal register path (mode 1) when every front fits one warp; QPDO_BATCH_FACTOR=columns forces
         // the column-by-column path (mode 0) for A/B tests
-        int mode = 1;
+        int mode = 1, max_front = 1;
         for (int sn = 0; sn < S->nsuper; sn++) {
             const int nc = S->sn_start[sn + 1] - S->sn_start[sn];
-            if (nc > SN_NCMAX || nc + S->sn_nr[sn] > SN_NMAX) mode = 0;
+            const int N = nc + S->sn_nr[sn];
+            if ((N - 1) * (N + 2) / 2 > BNT * SN_EPT || N > 254) mode = 0;
+            max_front = std::max(max_front, N);
         }
         { const char *ev = getenv("QPDO_BATCH_FACTOR"); if (ev && !strcmp(ev, "columns")) mode = 0; }
         std::vector<int> sn_f(S->nsuper), sn_nc(S->nsuper), sn_nr(S->nsuper), sn_base(S->nsuper), Sptr(S->nsuper + 1, 0), Srow, Uptr(S->nsuper + 1, 0), Upos;
@@ -919,6 +935,12 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             }
             return sn_base[sn] + jj * N - jj * (jj - 1) / 2 - jj + fr;
         };
+        std::vector<int> Eptr(S->nsuper + 1, 0), Emap;
+        for (int sn = 0; sn < S->nsuper; sn++) {
+            const int N = sn_nc[sn] + sn_nr[sn];
+            for (int j = 1; j < N; j++) for (int i = j; i <= N; i++) Emap.push_back(i | (j << 8));
+            Eptr[sn + 1] = (int)Emap.size();
+        }
         bool pattern_ok = true;
         for (int sn = 0; sn < S->nsuper; sn++) {
             const int nr = sn_nr[sn];
@@ -949,7 +971,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         memset(&P, 0, sizeof P);
         P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK;
         P.nKpack = mode == 1 ? b->lnz : n * (n + 1) / 2;
-        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode;
+        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front;
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
@@ -959,6 +981,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             b_upload(b, &P.Ktp, Ktp) || b_upload(b, &P.Kt_row, Kt_row) || b_upload(b, &P.Kt_a1, Kt_a1) || b_upload(b, &P.Kt_a2, Kt_a2) ||
             b_upload(b, &P.sn_f, sn_f) || b_upload(b, &P.sn_nc, sn_nc) || b_upload(b, &P.sn_nr, sn_nr) || b_upload(b, &P.sn_base, sn_base) ||
             b_upload(b, &P.Sptr, Sptr) || b_upload(b, &P.Srow, Srow) || b_upload(b, &P.Uptr, Uptr) || b_upload(b, &P.Upos, Upos) ||
+            b_upload(b, &P.Eptr, Eptr) || b_upload(b, &P.Emap, Emap) ||
             b_upload(b, &P.Kdiag, Kdiag) || b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
             break;
         P.max_iter = (int)s->max_iter; P.inner_max_iter = (int)s->inner_max_iter; P.proximal = (int)s->proximal; P.scaling = (int)s->scaling;
@@ -966,7 +989,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.eps_abs = s->eps_abs; P.eps_abs_in = s->eps_abs_in; P.eps_prim_inf = s->eps_prim_inf; P.eps_dual_inf = s->eps_dual_inf;
         P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
         P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
-        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8) + 2 * (size_t)m + 16;
+        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * ((size_t)max_front + 1)) + 2 * (size_t)m + 16;
         if (b->smem > 227 * 1024) {
             qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
             break;
