@@ -7,7 +7,7 @@ OUT=qpdo_b200/lib
 mkdir -p "$OUT" build
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 ARCH="-gencode arch=compute_100a,code=sm_100a"
-NVFLAGS="-O3 -std=c++17 -lineinfo $ARCH -Xcompiler -fPIC -fmad=false -Iinclude -I$SRC"
+NVFLAGS="-O3 -std=c++17 -lineinfo $ARCH -Xcompiler -fPIC -fmad=false -Iinclude -I$SRC $EXTRA_NVFLAGS"
 for f in dev_core dev_solver factor linesearch batch $EXTRA_CU; do
   [ -f "$SRC/$f.cu" ] || continue
   if [ ! -f build/$f.o ] || [ "$SRC/$f.cu" -nt build/$f.o ] || [ "$SRC/dev_internal.h" -nt build/$f.o ] || [ include/qpdo_cuda.h -nt build/$f.o ] || [ include/qpdo_batch.h -nt build/$f.o ]; then

@@ -70,6 +70,12 @@ int  qpdo_batch_solve_device(qpdo_batch *b, int count, const double *dQx, const 
 int  qpdo_batch_solve_data(const QPDOData *const *data, int count, const QPDOSettings *settings,
                            double *const *x, double *const *y, qpdo_batch_summary *summary, int device);
 
+/* diagnostics: per-phase clock64 accounting inside the batch kernel.  count == 0 switches it on for
+ * the following solves; count > 0 returns the mean SM cycles per instance of the last solve in
+ * cycles8[0..7] = { setup + scaling, residuals + outer updates, Newton preparation, K assembly,
+ * factorization + forward solve, backward solve, direction SpMVs, linesearch + iterate update }. */
+int  qpdo_batch_timing(qpdo_batch *b, int count, double *cycles8);
+
 /* diagnostics: shared memory per CTA, CTAs launched, nonzeros of L under the batch ordering */
 int  qpdo_batch_info(const qpdo_batch *b, int *smem_bytes, int *ctas, int *lnz, int *threads);
 

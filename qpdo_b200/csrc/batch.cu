@@ -24,6 +24,9 @@
 
 #define BNT 128                 // threads per CTA
 #define BNW (BNT / 32)
+#ifndef B_MINCTAS
+#define B_MINCTAS 4              // resident CTAs per SM the register budget is sized for
+#endif
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
 
@@ -35,8 +38,9 @@ struct BatchPlan {
     const int *Qp, *Qi;                      // lower CSC of Q
     const int *Fp, *Fj, *Fsrc, *Fdiag;       // full symmetric CSR of Q (split point per row)
     const int *perm;                         // perm[new] = old
-    const int *Kpos, *Kq, *Ktp, *Kt_row, *Kt_a1, *Kt_a2;     // K entries -> packed position, sources
-    const unsigned char *Kdiag;
+    int nKround;                             // K assembly: rounds of BNT entries
+    const int2 *Kround, *Kmeta;
+    const uint2 *Ktr;
     const int *Lcp, *Lri;                    // L column patterns (rows strictly below the diagonal)
     const int *Lrp, *Lci;                    // L row patterns (columns strictly left of the diagonal)
     // supernodal register path (mode 1): every front fits one warp (N + 1 <= 32 lanes)
@@ -45,8 +49,8 @@ struct BatchPlan {
     const int *sn_base;                      // offset of the packed trapezoid of each supernode in the L area
     const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
     const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
+    int max_front, ucolw;
     const int *Eptr, *Emap;                  // owned-entry enumeration of each front: i | j << 8, column major, j >= 1, i = j..N
-    int max_front;
     // settings (reference include/types.h:96-116)
     int max_iter, inner_max_iter, proximal, scaling, reset_newton_iter;
     double eps_abs, eps_abs_in, eps_prim_inf, eps_dual_inf, rho, theta, delta, mu_min, sigma_init, sigma_upd, sigma_min;
@@ -59,6 +63,7 @@ struct BatchIO {
     unsigned char *active;
     int count;
     int *next;                               // work queue head
+    long long *timing;                       // [count][8] clock64 cycles per phase (diagnostics) or NULL
 };
 
 // ------------------------------------------------------------------------------- block reductions
@@ -156,13 +161,25 @@ __device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av,
 {
     for (int t = threadIdx.x; t < P.nKpack; t += BNT) K[t] = 0.0;
     __syncthreads();
-    for (int e = threadIdx.x; e < P.nnzK; e += BNT) {
+    // entries are dealt to the threads in rounds of BNT (sorted by their number of contributing products);
+    // the products of round r sit slot-major, so that a warp reads 32 consecutive 8-byte records per slot
+    // and the slot loop has a uniform trip count (loads of several slots in flight)
+    for (int r = 0; r < P.nKround; r++) {
+        const int2 rk = P.Kround[r];                          // first slot, slots
+        const uint2 *T = P.Ktr + (size_t)rk.x * BNT + threadIdx.x;
         double v = 0.0;
-        for (int t = P.Ktp[e]; t < P.Ktp[e + 1]; t++) v = fma(om[P.Kt_row[t]], Av[P.Kt_a1[t]] * Av[P.Kt_a2[t]], v);
-        const int q = P.Kq[e];
-        if (q >= 0) v += Qv[q];
-        if (P.proximal && P.Kdiag[e]) v += sigma;
-        K[P.Kpos[e]] = v;
+#pragma unroll 4
+        for (int k = 0; k < rk.y; k++) {
+            const uint2 w = T[(size_t)k * BNT];               // row (or -1: padding), a1 | a2 << 16
+            if ((int)w.x >= 0) v = fma(om[w.x], Av[w.y & 0xffffu] * Av[w.y >> 16], v);
+        }
+        const int e = r * BNT + threadIdx.x;
+        if (e < P.nnzK) {
+            const int2 mt = P.Kmeta[e];                       // packed position | diagonal flag << 31, index into Q's values or -1
+            if (mt.y >= 0) v += Qv[mt.y];
+            if (P.proximal && mt.x < 0) v += sigma;
+            K[mt.x & 0x7fffffff] = v;
+        }
     }
     __syncthreads();
 }
@@ -217,9 +234,11 @@ __device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, 
 // the ucol / lcol buffers, barrier, every owner applies a_ij = fma(-u_i, l_j, a_ij), barrier.  No index
 // loads and no address arithmetic on the critical path.  Per entry the sequence of fma's is the one
 // b_factor_forward performs (ascending k, same operands): both paths give bit-identical results.
+// (A register-tile variant with one barrier per pivot and a shuffle-based single-warp variant were
+// measured slower on B200)
 #define SN_NMAX 31              // b_backward_sn: front order limit (one lane per front row)
-#define SN_EPT 8                // owned entries per thread: fronts up to (N - 1)(N + 2) / 2 <= BNT * SN_EPT
 __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + jj * N - ((jj * (jj - 1)) >> 1) - jj; }   // + front row i
+#define SN_EPT 8
 __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
     const int tid = threadIdx.x;
@@ -466,11 +485,13 @@ __device__ double b_linesearch(const BatchPlan &P, const BVec &V)
 #define FOR_N(i) for (int i = threadIdx.x; i < n; i += BNT)
 #define FOR_M(i) for (int i = threadIdx.x; i < m; i += BNT)
 
+#define B_TICK(slot) if (io.timing) { const long long now_ = clock64(); tacc[slot] += now_ - tlast; tlast = now_; }
 __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BVec &V, const int b)
 {
     const int n = P.n, m = P.m, tid = threadIdx.x;
     const bool scaled = P.scaling > 0, proximal = P.proximal != 0;
     double *red = V.red;
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = io.timing ? clock64() : 0;     // setup, residuals+outer, newton prep, assemble, factor, backward, direction, linesearch+update
     // ---- load (qpdo_setup's deep copy, src/qpdo.c:100-109); infinite bounds clipped like qpdo.m:138-139
     for (int k = tid; k < P.nnzA; k += BNT) V.Av[k] = io.Ax[(size_t)b * P.nnzA + k];
     for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = io.Qx[(size_t)b * P.nnzQ + k];
@@ -543,6 +564,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
     double eps_in = P.eps_abs_in, tau = 0.0;
     sigma = P.sigma_init;
     int reset_newton = 1, iter, oter = 0, iter_old = 0, status = QPDO_UNSOLVED, n_active = 0;
+    B_TICK(0)
     double rpn = 0, rdn = 0, rpin = 0, rdin = 0;
     __syncthreads();
     for (iter = 0; iter < P.max_iter; iter++) {
@@ -691,6 +713,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             __syncthreads();
         } else {
             // ---- update_iterate (iteration.c:11-25): newton_direction (newton.c:13-91)
+            B_TICK(1)
             if (P.reset_newton_iter != 0 && iter % P.reset_newton_iter == 0) reset_newton = 1;
             int ca = 0, ce = 0, cl = 0, n_enter, n_leave;
             FOR_M(i) {
@@ -723,17 +746,21 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             }
             __syncthreads();
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
+            B_TICK(2)
             b_assemble(P, V.Av, V.Qv, V.om, sigma, V.K);            // ends with __syncthreads
             FOR_N(k) { const int o = P.perm[k]; V.tn[k] = -V.rdi[o] - V.Atdy[o]; }     // P * rhs (newton.c:43-45)
             __syncthreads();
+            B_TICK(3)
             if (P.mode == 1) {
                 b_factor_fronts(P, V.K, V.tn, V.ucol);
+                B_TICK(4)
                 if (tid < 32) { if (P.max_front <= SN_NMAX) b_backward_sn(P, V.K, V.tn); else b_backward_fronts(P, V.K, V.tn); }
                 __syncthreads();
             } else {
                 b_factor_forward(P, V.K, V.tn);
                 b_backward(P, V.K, V.tn);
             }
+            B_TICK(5)
             FOR_N(k) V.dx[P.perm[k]] = V.tn[k];
             __syncthreads();
             b_spmv_Q(P, V.Qv, V.dx, V.Qdx);
@@ -744,10 +771,12 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             __syncthreads();
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
             __syncthreads();
+            B_TICK(6)
             tau = b_linesearch(P, V);
             FOR_N(i) { V.x[i] = V.x[i] + tau * V.dx[i]; V.Qx[i] = V.Qx[i] + tau * V.Qdx[i]; V.Aty[i] = V.Aty[i] + tau * V.Atdy[i]; }
             FOR_M(i) { V.y[i] = V.y[i] + tau * V.dy[i]; V.Ax[i] = V.Ax[i] + tau * V.Adx[i]; }
             __syncthreads();
+            B_TICK(7)
         }
     }
     if (status == QPDO_UNSOLVED) status = QPDO_MAX_ITER_REACHED;
@@ -762,6 +791,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
     if (io.x) { FOR_N(i) io.x[(size_t)b * n + i] = scaled ? V.x[i] * V.D[i] : V.x[i]; }
     if (io.y) { FOR_M(i) { double v = V.y[i]; if (scaled) { v = v * cinv; v = v * V.E[i]; } io.y[(size_t)b * m + i] = v; } }
     if (io.active) { FOR_M(i) io.active[(size_t)b * m + i] = V.act[i]; }
+    if (io.timing && tid == 0) { B_TICK(1) for (int j = 0; j < 8; j++) io.timing[(size_t)b * 8 + j] = tacc[j]; }
     if (io.summary && tid == 0) {
         qpdo_batch_summary s;
         s.status_val = status; s.iterations = iter; s.oterations = oter; s.n_active = n_active;
@@ -771,7 +801,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
 }
 
 // ------------------------------------------------------------------------------- kernel
-__global__ void __launch_bounds__(BNT, 4) k_batch_solve(const BatchPlan P, const BatchIO io)
+__global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const BatchPlan P, const BatchIO io)
 {
     extern __shared__ double sm[];
     __shared__ int s_b;
@@ -787,7 +817,7 @@ __global__ void __launch_bounds__(BNT, 4) k_batch_solve(const BatchPlan P, const
 #undef TAKE
     V.K = p; p += P.karea;
     V.red = p; p += BNW * 8;
-    V.ucol = p; p += 2 * (P.max_front + 1);
+    V.ucol = p; p += 2 * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
     for (;;) {
         __syncthreads();
@@ -813,6 +843,7 @@ struct qpdo_batch {
     qpdo_batch_summary *dsum = nullptr;
     unsigned char *dact = nullptr;
     int *next = nullptr;
+    long long *timing = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
 };
 
@@ -955,6 +986,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         if (!pattern_ok) mode = 0;
         // K entries -> packed positions
         const int nnzK = (int)S->nnzK;
+        int P_nKround = 0;
         std::vector<int> Kpos(nnzK), Kq(S->Kq, S->Kq + nnzK), Ktp(nnzK + 1);
         std::vector<unsigned char> Kdiag(nnzK);
         for (int k = 0; k < n && mode == 1; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++)
@@ -965,31 +997,60 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             Kdiag[e] = (i == k);
         }
         for (int e = 0; e <= nnzK; e++) Ktp[e] = (int)S->Ktp[e];
-        std::vector<int> Kt_row(S->Kt_row, S->Kt_row + S->ntriple), Kt_a1(S->Kt_a1, S->Kt_a1 + S->ntriple), Kt_a2(S->Kt_a2, S->Kt_a2 + S->ntriple);
+        // assembly program: entries sorted by product count, dealt in rounds of BNT, products slot-major per round
+        std::vector<int2> Kround, Kmeta(nnzK);
+        std::vector<uint2> Ktr;
+        {
+            std::vector<int> order(nnzK);
+            for (int e = 0; e < nnzK; e++) order[e] = e;
+            std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return Ktp[x + 1] - Ktp[x] > Ktp[y + 1] - Ktp[y]; });
+            const int nround = (nnzK + BNT - 1) / BNT;
+            for (int r = 0; r < nround; r++) {
+                int kmax = 0;
+                for (int t = 0; t < BNT && r * BNT + t < nnzK; t++) { const int e = order[r * BNT + t]; kmax = std::max(kmax, Ktp[e + 1] - Ktp[e]); }
+                int2 rk; rk.x = (int)(Ktr.size() / BNT); rk.y = kmax;
+                Kround.push_back(rk);
+                const size_t base = Ktr.size();
+                uint2 pad; pad.x = 0xffffffffu; pad.y = 0;
+                Ktr.resize(base + (size_t)kmax * BNT, pad);
+                for (int t = 0; t < BNT && r * BNT + t < nnzK; t++) {
+                    const int e = order[r * BNT + t];
+                    for (int k = 0; k < Ktp[e + 1] - Ktp[e]; k++) {
+                        const int64_t tt = S->Ktp[e] + k;
+                        uint2 w; w.x = (unsigned)S->Kt_row[tt]; w.y = (unsigned)S->Kt_a1[tt] | ((unsigned)S->Kt_a2[tt] << 16);
+                        Ktr[base + (size_t)k * BNT + t] = w;
+                    }
+                    int2 mt; mt.x = Kpos[e] | (Kdiag[e] ? (int)0x80000000 : 0); mt.y = Kq[e];
+                    Kmeta[r * BNT + t] = mt;
+                }
+            }
+            P_nKround = nround;
+        }
+        if (nnzA >= 65536) { qpdo_set_error("qpdo_batch_create: nnz(A) >= 65536 does not fit the batch kernel"); break; }
         std::vector<int> perm(S->perm, S->perm + n), vQp(Qp, Qp + n + 1), vQi(Qi, Qi + nnzQ), vAp(Ap, Ap + n + 1), vAi(Ai, Ai + nnzA);
         BatchPlan &P = b->P;
         memset(&P, 0, sizeof P);
         P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK;
         P.nKpack = mode == 1 ? b->lnz : n * (n + 1) / 2;
-        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front;
+        P.nKround = P_nKround;
+        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = max_front + 2;
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
         if (b_upload(b, &P.Ap, vAp) || b_upload(b, &P.Ai, vAi) || b_upload(b, &P.Rp, Rp) || b_upload(b, &P.Rj, Rj) || b_upload(b, &P.Rsrc, Rsrc) ||
             b_upload(b, &P.Qp, vQp) || b_upload(b, &P.Qi, vQi) || b_upload(b, &P.Fp, Fp) || b_upload(b, &P.Fj, Fj) || b_upload(b, &P.Fsrc, Fsrc) ||
-            b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kpos, Kpos) || b_upload(b, &P.Kq, Kq) ||
-            b_upload(b, &P.Ktp, Ktp) || b_upload(b, &P.Kt_row, Kt_row) || b_upload(b, &P.Kt_a1, Kt_a1) || b_upload(b, &P.Kt_a2, Kt_a2) ||
+            b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kround, Kround) || b_upload(b, &P.Kmeta, Kmeta) || b_upload(b, &P.Ktr, Ktr) ||
             b_upload(b, &P.sn_f, sn_f) || b_upload(b, &P.sn_nc, sn_nc) || b_upload(b, &P.sn_nr, sn_nr) || b_upload(b, &P.sn_base, sn_base) ||
             b_upload(b, &P.Sptr, Sptr) || b_upload(b, &P.Srow, Srow) || b_upload(b, &P.Uptr, Uptr) || b_upload(b, &P.Upos, Upos) ||
             b_upload(b, &P.Eptr, Eptr) || b_upload(b, &P.Emap, Emap) ||
-            b_upload(b, &P.Kdiag, Kdiag) || b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
+            b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
             break;
         P.max_iter = (int)s->max_iter; P.inner_max_iter = (int)s->inner_max_iter; P.proximal = (int)s->proximal; P.scaling = (int)s->scaling;
         P.reset_newton_iter = (int)s->reset_newton_iter;
         P.eps_abs = s->eps_abs; P.eps_abs_in = s->eps_abs_in; P.eps_prim_inf = s->eps_prim_inf; P.eps_dual_inf = s->eps_dual_inf;
         P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
         P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
-        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * ((size_t)max_front + 1)) + 2 * (size_t)m + 16;
+        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * (size_t)P.ucolw) + 2 * (size_t)m + 16;
         if (b->smem > 227 * 1024) {
             qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
             break;
@@ -1025,7 +1086,7 @@ extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *d
     CUDA_OK(cudaSetDevice(b->device));
     BatchIO io;
     io.Qx = dQx; io.Ax = dAx; io.q = dq; io.l = dl; io.u = du; io.c = dc; io.x0 = dx0; io.y0 = dy0;
-    io.x = dx; io.y = dy; io.summary = dsummary; io.active = dactive; io.count = count; io.next = b->next;
+    io.x = dx; io.y = dy; io.summary = dsummary; io.active = dactive; io.count = count; io.next = b->next; io.timing = b->timing;
     CUDA_OK(cudaMemsetAsync(b->next, 0, sizeof(int), b->st));
     if (kernel_ms) CUDA_OK(cudaEventRecord(b->e0, b->st));
     const int grid = std::min(count, b->ctas);
@@ -1064,6 +1125,20 @@ extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, cons
     if (active_set && m) CUDA_OK(cudaMemcpyAsync(active_set, b->dact, cn * m, cudaMemcpyDeviceToHost, b->st));
     cudaError_t e = cudaStreamSynchronize(b->st);
     if (e != cudaSuccess) { qpdo_set_error("batch kernel failed: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+extern "C" int qpdo_batch_timing(qpdo_batch *b, int count, double *cycles8)
+{   // count == 0: switch the per-phase clock64 accounting on; count > 0: mean cycles per instance and phase of the last solve
+    if (!b) return -3;
+    CUDA_OK(cudaSetDevice(b->device));
+    if (!b->timing) { if (b_alloc(b, &b->timing, (size_t)b->capacity * 8)) return -1; CUDA_OK(cudaMemset(b->timing, 0, sizeof(long long) * 8 * b->capacity)); }
+    if (count <= 0 || !cycles8) return 0;
+    if (count > b->capacity) count = b->capacity;
+    std::vector<long long> h((size_t)count * 8);
+    CUDA_OK(cudaStreamSynchronize(b->st));
+    CUDA_OK(cudaMemcpy(h.data(), b->timing, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost));
+    for (int j = 0; j < 8; j++) { double sacc = 0; for (int i = 0; i < count; i++) sacc += (double)h[(size_t)i * 8 + j]; cycles8[j] = sacc / count; }
     return 0;
 }
 

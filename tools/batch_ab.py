@@ -25,3 +25,19 @@ print("x bitwise equal:", np.array_equal(xa, xb), " y:", np.array_equal(ya, yb),
 print("max |dx|", np.abs(xa - xb).max(), "iteration mismatches", int((sa["iterations"] != sb["iterations"]).sum()))
 assert np.array_equal(xa, xb) and np.array_equal(ya, yb) and np.array_equal(sa, sb) and np.array_equal(aa, ab)
 print("AB_OK")
+
+# per-phase cycle accounting (qpdo_batch_timing) of the front paths
+import ctypes as C
+names = ["setup+scaling", "residuals+outer", "newton prep", "K assembly", "factor+forward", "backward", "direction spmv", "linesearch+update"]
+for mode in ("supernodes",):
+    os.environ["QPDO_BATCH_FACTOR"] = mode
+    bt, vals = qbatch.from_mpc(b)
+    bt.lib.qpdo_batch_timing.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
+    bt.lib.qpdo_batch_timing(bt.h, 0, None)
+    r = bt.solve(*vals)
+    assert np.array_equal(r[0], xa), mode
+    cyc = (C.c_double * 8)()
+    bt.lib.qpdo_batch_timing(bt.h, B, cyc)
+    tot = sum(cyc)
+    print(mode, " ".join("%s %.0fk (%.0f%%)" % (nm, c / 1e3, 100 * c / tot) for nm, c in zip(names, cyc)), "| total %.0fk cycles/QP" % (tot / 1e3))
+    bt.destroy()
