@@ -267,17 +267,27 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
                 const int i = k + 1 + tid;
                 double *pa = (i < N) ? L + pc + i : xs + f + k;
                 const double u = *pa, dk = L[pc + k];
-                const double l = u / dk;
+                // u / dk, correctly rounded (Markstein: reciprocal, product, one residual correction).  The plain
+                // quotient takes DDIV's ~60-instruction slow path whenever u == 0, which structural zeros of
+                // the front make the common case; this form never does and gives the same bits.
+                const double rk = __drcp_rn(dk), q0 = __dmul_rn(u, rk);
+                const double l = fma(fma(-q0, dk, u), rk, q0);
                 ucol[i] = u; lcol[i] = l; *pa = l;
             }
             __syncthreads();
+            // all loads first, then the fma's, then the stores: the owned entries are independent, the
+            // compiler cannot know that (everything is a double* into shared memory)
+            double uv[SN_EPT], lv[SN_EPT], av[SN_EPT];
 #pragma unroll
             for (int e = 0; e < SN_EPT; e++) {
-                if (e < ept) {
-                    const int i = eij[e] & 255, j = eij[e] >> 8;
-                    if (j > k) *ea[e] = fma(-ucol[i], lcol[j], *ea[e]);
-                }
+                const bool on = e < ept && (eij[e] >> 8) > k;
+                uv[e] = on ? ucol[eij[e] & 255] : 0.0; lv[e] = on ? lcol[eij[e] >> 8] : 0.0; av[e] = on ? *ea[e] : 0.0;
             }
+#pragma unroll
+            for (int e = 0; e < SN_EPT; e++) av[e] = fma(-uv[e], lv[e], av[e]);
+#pragma unroll
+            for (int e = 0; e < SN_EPT; e++)
+                if (e < ept && (eij[e] >> 8) > k) *ea[e] = av[e];
             __syncthreads();
         }
     }
