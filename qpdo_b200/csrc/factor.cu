@@ -292,11 +292,23 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
             if (lane < nb) { yb[lane] = v; A.xs[f + kb + lane] = v / D[lane][lane]; }
         }
         __syncthreads();
+        // rows below the block: one row per thread, its NB panel entries fetched as two batches of 16
+        // independent loads (the panel streams from HBM/L2 once; latency, not bandwidth, bounds one CTA)
         for (int i = kb + nb + tid; i < N; i += NT) {
             const double *Li = L + (int64_t)kb * N + i;
             double acc = 0.0;
-#pragma unroll 8
-            for (int k = 0; k < nb; k++) acc = fma(Li[(int64_t)k * N], yb[k], acc);
+            if (nb == NB) {
+#pragma unroll
+                for (int h = 0; h < NB; h += 16) {
+                    double lv[16];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) lv[k] = __ldg(Li + (int64_t)(h + k) * N);
+#pragma unroll
+                    for (int k = 0; k < 16; k++) acc = fma(lv[k], yb[h + k], acc);
+                }
+            } else {
+                for (int k = 0; k < nb; k++) acc = fma(Li[(int64_t)k * N], yb[k], acc);
+            }
             vec[i] -= acc;
         }
         __syncthreads();
@@ -325,7 +337,15 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
         for (int k = wid; k < nb; k += NW) {
             const double *Lk = L + (int64_t)(kb + k) * N;
             double acc = 0.0;
-            for (int i = kb + nb + lane; i < N; i += 32) acc = fma(Lk[i], vec[i], acc);
+            int i = kb + nb + lane;
+            for (; i + 7 * 32 < N; i += 8 * 32) {            // 8 independent loads in flight per lane
+                double lv[8];
+#pragma unroll
+                for (int r = 0; r < 8; r++) lv[r] = __ldg(Lk + i + r * 32);
+#pragma unroll
+                for (int r = 0; r < 8; r++) acc = fma(lv[r], vec[i + r * 32], acc);
+            }
+            for (; i < N; i += 32) acc = fma(Lk[i], vec[i], acc);
             for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
             if (lane == 0) vec[kb + k] -= acc;
         }
@@ -354,6 +374,7 @@ __global__ void k_permute_out(const double *xs, const int *perm, double *x, int 
 
 // =============================================================================== host side
 static const int BUCKET_N[4] = {32, 64, 104, 150};       // smem-front size classes (front order N)
+static const int SOLVE_BIG_N = 256;                       // fronts above this order are solved by 1024 threads
 static const int SOLVE_WARP_N = 64;                       // fronts up to this order are solved by one warp
 
 static FArgs fargs(qpdo_dev *d)
@@ -487,9 +508,21 @@ static long issue_solve(qpdo_dev *d)
             while (q < e && ordN(q) > SOLVE_WARP_N) q++;
             if (q > b) {
                 size_t smem = sizeof(double) * (ordN(b) + NB);
-                if (pass == 0) k_fwd<256><<<q - b, 256, smem, d->st>>>(A, F.level_sn + b);
-                else k_bwd<256><<<q - b, 256, smem, d->st>>>(A, F.level_sn + b);
-                launches++;
+                // fronts wider than SOLVE_BIG_N rows get 1024 threads (one panel row / one panel column per
+                // thread / warp), the rest of the CTA-solved fronts 256
+                int qb = b;
+                while (qb < q && ordN(qb) > SOLVE_BIG_N) qb++;
+                if (qb > b) {
+                    if (pass == 0) k_fwd<1024><<<qb - b, 1024, smem, d->st>>>(A, F.level_sn + b);
+                    else k_bwd<1024><<<qb - b, 1024, smem, d->st>>>(A, F.level_sn + b);
+                    launches++;
+                }
+                if (q > qb) {
+                    smem = sizeof(double) * (ordN(qb) + NB);
+                    if (pass == 0) k_fwd<256><<<q - qb, 256, smem, d->st>>>(A, F.level_sn + qb);
+                    else k_bwd<256><<<q - qb, 256, smem, d->st>>>(A, F.level_sn + qb);
+                    launches++;
+                }
             }
             if (e > q) {
                 size_t smem = sizeof(double) * (ordN(q) + NB);
