@@ -48,6 +48,15 @@ __global__ void k_products(int64_t nt, const int *a1, const int *a2, const doubl
     if (t < nt) val[t] = Ax[a1[t]] * Ax[a2[t]];
 }
 
+// u / d for a pivot d whose correctly rounded reciprocal r = __drcp_rn(d) is at hand: q0 = u r, one residual
+// correction (Markstein) gives the correctly rounded quotient, i.e. the same bits as u / d, without the
+// ~60-instruction slow path that DDIV takes for every zero numerator (structural zeros of a front).
+__device__ __forceinline__ double div_by_pivot(double u, double d, double r)
+{
+    const double q0 = __dmul_rn(u, r);
+    return fma(fma(-q0, d, u), r, q0);
+}
+
 // ------------------------------------------------------------------------------- smem fronts
 // One CTA per front: load the panel, extend-add the children's update matrices in fixed order,
 // eliminate the nc pivot columns (right-looking), write the panel and the Schur complement.
@@ -72,17 +81,39 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
         }
         __syncthreads();
     }
-    const int lane = tid & 31, wid = tid >> 5, NW = NT / 32;
-    // right-looking LDL': column k stays unscaled (= L D) while it updates the trailing matrix
+    // right-looking LDL', two phases per pivot: (A) the rows below the pivot compute l_i = a_ik / d_k into
+    // lcol (column k itself stays unscaled = L D while it updates), (B) the trailing lower triangle is
+    // dealt flat to all threads: a_ij = fma(-a_ik, l_j, a_ij).  Same fma sequence per entry as a
+    // column-by-column elimination.
+    double *lcol = F + (size_t)ld * N, *ucol = lcol + N;
     for (int k = 0; k < nc; k++) {
         const double dk = F[k + k * ld];
         if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
-        for (int j = k + 1 + wid; j < N; j += NW) {
-            const double ljk = F[j + k * ld] / dk;
-            for (int i = j + lane; i < N; i += 32) F[i + j * ld] = fma(-F[i + k * ld], ljk, F[i + j * ld]);
+        const double rk = __drcp_rn(dk);
+        for (int i = k + 1 + tid; i < N; i += NT) {
+            const double u = F[i + k * ld], l = div_by_pivot(u, dk, rk);
+            ucol[i] = u; lcol[i] = l; F[i + k * ld] = l;
         }
         __syncthreads();
-        for (int i = k + 1 + tid; i < N; i += NT) F[i + k * ld] = F[i + k * ld] / dk;
+        const int R = N - k - 1;                           // trailing order; columns j = k+1+jj, rows i = j..N-1
+        for (int jj = 0; jj < R; jj++) {
+            // column jj has R - jj entries; short columns are batched below
+            if (R - jj < NT / 2) break;
+            const int j = k + 1 + jj;
+            const double lj = lcol[j];
+            for (int i = j + tid; i < N; i += NT) F[i + j * ld] = fma(-ucol[i], lj, F[i + j * ld]);
+        }
+        {   // remaining short columns: flat index over the (rows x columns) rectangle, upper part skipped
+            int jj0 = 0;
+            while (jj0 < R && R - jj0 >= NT / 2) jj0++;
+            const int C = R - jj0, H = R - jj0;              // C columns, the tallest has H entries
+            for (int idx = tid; idx < C * H; idx += NT) {
+                const int c = idx / H, r = idx - c * H;
+                const int j = k + 1 + jj0 + c, i = j + r;
+                if (i < N) F[i + j * ld] = fma(-ucol[i], lcol[j], F[i + j * ld]);
+            }
+        }
+        __syncthreads();
     }
     __syncthreads();
     for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; Lp[idx] = (i >= j) ? F[i + j * ld] : 0.0; }
@@ -141,16 +172,21 @@ __global__ void __launch_bounds__(256) k_big_potrf(FArgs A, const int *list, int
     double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N + kb;
     for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; D[i][j] = Lb[(int64_t)j * N + i]; }
     __syncthreads();
-    const int lane = tid & 31, wid = tid >> 5;
-    for (int k = 0; k < nb; k++) {
+    __shared__ double uc[NB], lc[NB];
+    for (int k = 0; k < nb; k++) {                  // two phases per pivot, as in k_front_smem
         const double dk = D[k][k];
         if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
-        for (int j = k + 1 + wid; j < nb; j += 8) {
-            const double ljk = D[j][k] / dk;
-            if (lane >= j && lane < nb) D[lane][j] = fma(-D[lane][k], ljk, D[lane][j]);
+        if (tid > k && tid < nb) {
+            const double u = D[tid][k], l = div_by_pivot(u, dk, __drcp_rn(dk));
+            uc[tid] = u; lc[tid] = l; D[tid][k] = l;
         }
         __syncthreads();
-        if (tid > k && tid < nb) D[tid][k] = D[tid][k] / dk;
+        const int R = nb - k - 1;
+        for (int idx = tid; idx < R * R; idx += 256) {
+            const int c = idx / R, r = idx - c * R;
+            if (r >= c) D[k + 1 + r][k + 1 + c] = fma(-uc[k + 1 + r], lc[k + 1 + c], D[k + 1 + r][k + 1 + c]);
+        }
+        __syncthreads();
     }
     __syncthreads();
     for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; Lb[(int64_t)j * N + i] = (i >= j) ? D[i][j] : 0.0; }
@@ -170,6 +206,9 @@ __global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int 
         int j = idx / NB, i = idx - j * NB;
         D[i][j] = (i < nb && j < nb) ? Lb[(int64_t)j * N + kb + i] : (i == j ? 1.0 : 0.0);
     }
+    __shared__ double Rinv[NB];
+    __syncthreads();
+    if (tid < NB) Rinv[tid] = __drcp_rn(D[tid][tid]);
     __syncthreads();
     const int i = r0 + tid;
     if (i >= N) return;
@@ -185,7 +224,7 @@ __global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int 
         x[j] = v;
     }
 #pragma unroll
-    for (int j = 0; j < NB; j++) x[j] = x[j] / D[j][j];
+    for (int j = 0; j < NB; j++) x[j] = div_by_pivot(x[j], D[j][j], Rinv[j]);
 #pragma unroll
     for (int j = 0; j < NB; j++) if (j < nb) Lb[(int64_t)j * N + i] = x[j];
 }
@@ -485,7 +524,7 @@ static long issue_factor(qpdo_dev *d)
                     }
                 }
             } else {
-                size_t smem = sizeof(double) * (size_t)(L.maxN | 1) * L.maxN;
+                size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 2 * (size_t)L.maxN);
                 if (L.maxnc == 0) k_front_smem<64><<<L.count, 64, smem, d->st>>>(A, list);
                 else if (L.maxnc == 1) k_front_smem<128><<<L.count, 128, smem, d->st>>>(A, list);
                 else k_front_smem<256><<<L.count, 256, smem, d->st>>>(A, list);
