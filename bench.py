@@ -230,6 +230,157 @@ def ref_c3(args, sample_iters=12):
             (iters, N, "CHOLMOD supernodal + OpenBLAS" if kind == "reference" else "C restatement"), "wall_s": time.time() - t0}
 
 
+# ------------------------------------------------------------------------------------------ C5
+from qpdo_b200 import batch as qbatch      # ctypes mirror of include/qpdo_batch.h (no compute of its own)
+import ctypes as C
+
+C5_BATCH = 65536
+
+
+def algorithmic_bytes_per_qp(n, m, nnzQ, nnzA):
+    """HBM bytes one instance must move: its values in (Qx, Ax, q, l, u), its results out (x, y, summary,
+    active set).  The whole solver loop in between lives in shared memory (batch kernel)."""
+    return 8 * (nnzQ + nnzA + n + 2 * m) + 8 * (n + m) + 40 + m
+
+
+def c5_config(B, n, m, nnzA, world):
+    per_rank = (B + world - 1) // world
+    return {"workload": "c5: %d MPC QPs (n=%d, m=%d, nnzA=%d, common pattern), contiguous blocks over %d rank(s); "
+                        "inputs %.0f MB per rank vs 126 MB L2" % (B, n, m, nnzA, world, 8e-6 * per_rank * (n + nnzA + n + 2 * m)),
+            "batch": B, "n": n, "m": m, "nnzA": nnzA, "per_rank": per_rank}
+
+
+def run_c5(args, dist):
+    """C5 arm of bench.py: the whole batch (BASELINE configs[4]) partitioned in contiguous blocks over
+    the ranks; a step = every rank solving its block once.  `value`: inputs resident in HBM, device
+    pointers through qpdo_batch_solve_device.  `e2e`: qpdo_batch_solve with pinned HOST buffers."""
+    import torch
+    from qpdo_b200 import problems
+    B = args.size or C5_BATCH
+    lo, hi = qbatch.partition(B, dist.world, dist.rank)
+    cnt = hi - lo
+    torch.cuda.set_device(dist.local)
+    b = problems.mpc_batch(cnt, first=lo)
+    bt, vals = qbatch.from_mpc(b, capacity=cnt, device=dist.local)
+    n, m, nnzQ, nnzA = bt.n, bt.m, bt.nnzQ, bt.nnzA
+    info = bt.info()
+    # pinned host buffers (the e2e leg) and device-resident copies (the value leg)
+    host = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for v in vals]
+    dev = [h.cuda(non_blocking=False) for h in host]
+    dx = torch.empty((cnt, n), dtype=torch.float64, device="cuda")
+    dy = torch.empty((cnt, m), dtype=torch.float64, device="cuda")
+    dsum = torch.zeros((cnt, 40), dtype=torch.uint8, device="cuda")
+    dact = torch.zeros((cnt, m), dtype=torch.uint8, device="cuda")
+    hx = torch.empty((cnt, n), dtype=torch.float64).pin_memory()
+    hy = torch.empty((cnt, m), dtype=torch.float64).pin_memory()
+    hsum = torch.zeros((cnt, 40), dtype=torch.uint8).pin_memory()
+    hact = torch.zeros((cnt, m), dtype=torch.uint8).pin_memory()
+    torch.cuda.synchronize()
+    ptrs = [t.data_ptr() for t in dev] + [0, 0, 0]                       # c, x0, y0 = NULL
+    outs = [dx.data_ptr(), dy.data_ptr(), dsum.data_ptr(), dact.data_ptr()]
+
+    def step_device():
+        return bt.solve_device(cnt, ptrs, outs, kernel_ms=True)
+
+    def step_host():
+        rc = bt.lib.qpdo_batch_solve(bt.h, cnt, *[C.cast(h.data_ptr(), qbatch._pd) for h in host], None, None, None,
+                                     C.cast(hx.data_ptr(), qbatch._pd), C.cast(hy.data_ptr(), qbatch._pd), hsum.data_ptr(), hact.data_ptr())
+        if rc:
+            raise RuntimeError("qpdo_batch_solve failed: %s" % bt.lib.qpdo_dev_last_error().decode())
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    torch.cuda.synchronize(); dist.barrier()
+    kern_ms = []
+    with ClockSampler(dist.local) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            kern_ms.append(step_device())
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+    dist.barrier()
+    dev_ms = float(np.sum(kern_ms))                       # CUDA events on the batch's own stream
+    step_host()                                           # e2e warm-up
+    torch.cuda.synchronize(); dist.barrier()
+    e2e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()
+    e2e_wall = time.perf_counter() - t0
+    dist.barrier()
+    # status / objective summaries: the only inter-rank traffic (SURVEY 8(e)), 40 B per QP
+    summ = dsum.cpu().numpy().view(qbatch.SUMMARY_DTYPE).reshape(-1)
+    pad = np.zeros(((B + dist.world - 1) // dist.world) * 40, dtype=np.uint8)
+    pad[:cnt * 40] = summ.view(np.uint8)
+    allsum = dist.gather_bytes(pad)
+    parts = []
+    for r, a in enumerate(allsum):
+        l2, h2 = qbatch.partition(B, dist.world, r)
+        parts.append(a[:(h2 - l2) * 40].view(qbatch.SUMMARY_DTYPE))
+    allsum = np.concatenate(parts)
+    # the host-buffer leg must reproduce the device leg bit for bit
+    same = bool(np.array_equal(hsum.numpy().view(qbatch.SUMMARY_DTYPE).reshape(-1)["iterations"], summ["iterations"]))
+    worst = dist.reduce([dev_ms, wall * 1e3, e2e_wall * 1e3], "max")
+    total_iter = dist.reduce([float(summ["iterations"].sum())], "sum")[0]
+    pk, pk_src = peaks()
+    bytes_qp = algorithmic_bytes_per_qp(n, m, nnzQ, nnzA)
+    k_ms = worst[0] / args.steps
+    rl = {"bound": "hbm", "kernel": "k_batch_solve (one CTA per QP, solver loop in shared memory)",
+          "achieved": bytes_qp * cnt / (k_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s",
+          "traffic": None, "bytes_per_qp": bytes_qp,
+          "note": "HBM is touched only to load an instance and store its result; the %d loop passes per QP run in shared memory "
+                  "(latency/issue-bound, see profiles/)" % round(total_iter / B)}
+    rl["frac"] = rl["achieved"] / rl["peak"]
+    h2d = 8 * cnt * (nnzQ + nnzA + n + 2 * m)
+    d2h = cnt * (8 * (n + m) + 40 + m)
+    out = {"metric": qbatch.METRIC, "value": B * args.steps / (worst[1] * 1e-3), "unit": "QP/s", "n_gpus": dist.world, "steps": args.steps,
+           "warmup": max(args.warmup, 3), "ms_per_step": worst[1] / args.steps, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": c5_config(B, n, m, nnzA, dist.world),
+           "kernel_ms_per_step": k_ms, "kernel_qp_per_s": B / (k_ms * 1e-3),
+           "batch_kernel": dict(info, mean_iterations=total_iter / B),
+           "result": {"solved": int((allsum["status_val"] == 1).sum()), "primal_infeasible": int((allsum["status_val"] == -3).sum()),
+                      "dual_infeasible": int((allsum["status_val"] == -4).sum()), "max_iter_reached": int((allsum["status_val"] == -2).sum()),
+                      "objective_sum": float(allsum["objective"][allsum["status_val"] == 1].sum()), "host_leg_matches_device_leg": same},
+           "roofline": rl,
+           "e2e": {"value": B * e2e_steps / (worst[2] * 1e-3), "unit": "QP/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "call": "qpdo_batch_solve (pinned host buffers in, x / y / summary / active set out)"},
+           "gpu_launches": args.steps, "clocks": clk.summary()}
+    bt.destroy()
+    return out
+
+
+def ref_c5(args, bounded=True):
+    """The reference's own CPU path for C5: the per-problem qpdo_setup / qpdo_solve / qpdo_cleanup loop
+    (oracle/ref_batch.c over oracle/_ref/libqpdo_ref.so) on all host cores, over a bounded sample
+    of the same instances."""
+    import oracle
+    from qpdo_b200 import problems
+    ncores = os.cpu_count() or 1
+    sample = min(args.size or C5_BATCH, 2048 * max(1, ncores // 4))
+    b = problems.mpc_batch(sample)
+    n, m = b["n"], b["m"]
+    Qp = np.arange(n + 1); Qi = np.arange(n); Qx = np.tile(b["Qd"], (sample, 1))
+    if oracle.have_ref():
+        kind = "reference"
+        best = None
+        for _ in range(max(1, min(getattr(args, "steps", 1) or 1, 3))):
+            secs, summ = oracle.ref_batch_loop(n, m, Qp, Qi, b["Ap"], b["Ai"], Qx, b["Ax"], b["q"], b["l"], b["u"], threads=ncores)
+            best = secs if best is None else min(best, secs)
+        secs = best
+    else:
+        kind, ncores = "port", 1
+        sample = min(sample, 512)
+        t0 = time.perf_counter()
+        for i in range(sample):
+            oracle.solve(problems.mpc_instance(b, i), trace=False)
+        secs = time.perf_counter() - t0
+    return {"value": sample / secs, "unit": "QP/s", "cores": ncores, "kind": kind,
+            "sample": "first %d instances of the C5 batch, one qpdo_setup/qpdo_solve/qpdo_cleanup per QP, %d host thread(s)" % (sample, ncores),
+            "wall_s": secs}
+
+
+
 # ------------------------------------------------------------------------------------------ main
 def main():
     ap = argparse.ArgumentParser()
@@ -259,11 +410,16 @@ def main():
             line = {"impl": "reference", "metric": "KKT factor+solve ms per Newton iteration (CONT-%d-shaped QP)" % (args.size or C3_N),
                     "value": b["value"], "unit": "ms/iter", "higher_is_better": False}
         else:
-            from qpdo_b200 import batch as qbatch
-            b = qbatch.bench_reference(args)
+            b = ref_c5(args)
             line = {"impl": "reference", "metric": qbatch.METRIC, "value": b["value"], "unit": "QP/s", "higher_is_better": True}
+        if args.workload == "c5":
+            from qpdo_b200 import problems
+            pn, pm, prow = problems.mpc_pattern()[:3]
+            cfg = c5_config(args.size or C5_BATCH, pn, pm, int(prow.size), max(1, args.gpus))
+        else:
+            cfg = {"workload": "c3: CONT-%d-like banded PDE-constraint QP, bounded sample of one solve" % (args.size or C3_N)}
         line.update({"n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "scaling": "strong" if args.workload == "c5" else "replicas",
-                     "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": args.workload},
+                     "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
                      "cpu_baseline": b, "e2e": {"value": b["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
         print(json.dumps(line))
         return 0
@@ -273,15 +429,14 @@ def main():
         if args.workload == "c3":
             out = run_c3(args, dist)
         else:
-            from qpdo_b200 import batch as qbatch
-            out = qbatch.bench(args, dist, ClockSampler, peaks)
+            out = run_c5(args, dist)
         if dist.rank == 0:
             if dist.world == 1 and not args.no_cpu_baseline:
                 try:
                     if args.workload == "c3":
                         out["cpu_baseline"] = ref_c3(args)
                     else:
-                        out["cpu_baseline"] = qbatch.bench_reference(args, bounded=True)
+                        out["cpu_baseline"] = ref_c5(args, bounded=True)
                 except Exception as e:          # the baseline is a reported number, never a reason to fail the bench
                     out["cpu_baseline"] = {"value": None, "error": repr(e)}
             print(json.dumps(out))

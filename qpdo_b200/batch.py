@@ -130,165 +130,3 @@ def from_mpc(batch, capacity=None, settings=None, device=-1):
     bt = Batch(n, m, Qp, Qi, batch["Ap"], batch["Ai"], capacity or B, settings, device)
     Qx = np.tile(batch["Qd"], (B, 1))
     return bt, (Qx, batch["Ax"], batch["q"], batch["l"], batch["u"])
-
-
-# ------------------------------------------------------------------------------------------ bench legs
-C5_BATCH = 65536
-
-
-def algorithmic_bytes_per_qp(n, m, nnzQ, nnzA):
-    """HBM bytes one instance must move: its values in (Qx, Ax, q, l, u), its results out (x, y, summary,
-    active set).  The whole solver loop in between lives in shared memory (batch kernel)."""
-    return 8 * (nnzQ + nnzA + n + 2 * m) + 8 * (n + m) + 40 + m
-
-
-def bench(args, dist, ClockSampler, peaks):
-    """C5 arm of bench.py: the whole batch (BASELINE configs[4]) partitioned in contiguous blocks over
-    the ranks; a step = every rank solving its block once.  `value`: inputs resident in HBM, device
-    pointers through qpdo_batch_solve_device.  `e2e`: qpdo_batch_solve with pinned HOST buffers."""
-    import torch
-    from . import problems
-    B = args.size or C5_BATCH
-    lo, hi = partition(B, dist.world, dist.rank)
-    cnt = hi - lo
-    torch.cuda.set_device(dist.local)
-    b = problems.mpc_batch(cnt, first=lo)
-    bt, vals = from_mpc(b, capacity=cnt, device=dist.local)
-    n, m, nnzQ, nnzA = bt.n, bt.m, bt.nnzQ, bt.nnzA
-    info = bt.info()
-    # pinned host buffers (the e2e leg) and device-resident copies (the value leg)
-    host = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for v in vals]
-    dev = [h.cuda(non_blocking=False) for h in host]
-    dx = torch.empty((cnt, n), dtype=torch.float64, device="cuda")
-    dy = torch.empty((cnt, m), dtype=torch.float64, device="cuda")
-    dsum = torch.zeros((cnt, 40), dtype=torch.uint8, device="cuda")
-    dact = torch.zeros((cnt, m), dtype=torch.uint8, device="cuda")
-    hx = torch.empty((cnt, n), dtype=torch.float64).pin_memory()
-    hy = torch.empty((cnt, m), dtype=torch.float64).pin_memory()
-    hsum = torch.zeros((cnt, 40), dtype=torch.uint8).pin_memory()
-    hact = torch.zeros((cnt, m), dtype=torch.uint8).pin_memory()
-    torch.cuda.synchronize()
-    ptrs = [t.data_ptr() for t in dev] + [0, 0, 0]                       # c, x0, y0 = NULL
-    outs = [dx.data_ptr(), dy.data_ptr(), dsum.data_ptr(), dact.data_ptr()]
-
-    def step_device():
-        return bt.solve_device(cnt, ptrs, outs, kernel_ms=True)
-
-    def step_host():
-        rc = bt.lib.qpdo_batch_solve(bt.h, cnt, *[C.cast(h.data_ptr(), _pd) for h in host], None, None, None,
-                                     C.cast(hx.data_ptr(), _pd), C.cast(hy.data_ptr(), _pd), hsum.data_ptr(), hact.data_ptr())
-        if rc:
-            raise RuntimeError("qpdo_batch_solve failed: %s" % bt.lib.qpdo_dev_last_error().decode())
-
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    torch.cuda.synchronize(); dist.barrier()
-    kern_ms = []
-    with ClockSampler(dist.local) as clk:
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            kern_ms.append(step_device())
-        torch.cuda.synchronize()
-        wall = time.perf_counter() - t0
-    dist.barrier()
-    dev_ms = float(np.sum(kern_ms))                       # CUDA events on the batch's own stream
-    step_host()                                           # e2e warm-up
-    torch.cuda.synchronize(); dist.barrier()
-    e2e_steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        step_host()
-    e2e_wall = time.perf_counter() - t0
-    dist.barrier()
-    # status / objective summaries: the only inter-rank traffic (SURVEY 8(e)), 40 B per QP
-    summ = dsum.cpu().numpy().view(SUMMARY_DTYPE).reshape(-1)
-    pad = np.zeros(((B + dist.world - 1) // dist.world) * 40, dtype=np.uint8)
-    pad[:cnt * 40] = summ.view(np.uint8)
-    allsum = dist.gather_bytes(pad)
-    parts = []
-    for r, a in enumerate(allsum):
-        l2, h2 = partition(B, dist.world, r)
-        parts.append(a[:(h2 - l2) * 40].view(SUMMARY_DTYPE))
-    allsum = np.concatenate(parts)
-    # the host-buffer leg must reproduce the device leg bit for bit
-    same = bool(np.array_equal(hsum.numpy().view(SUMMARY_DTYPE).reshape(-1)["iterations"], summ["iterations"]))
-    worst = dist.reduce([dev_ms, wall * 1e3, e2e_wall * 1e3], "max")
-    total_iter = dist.reduce([float(summ["iterations"].sum())], "sum")[0]
-    pk, pk_src = peaks()
-    bytes_qp = algorithmic_bytes_per_qp(n, m, nnzQ, nnzA)
-    k_ms = worst[0] / args.steps
-    rl = {"bound": "hbm", "kernel": "k_batch_solve (one CTA per QP, solver loop in shared memory)",
-          "achieved": bytes_qp * cnt / (k_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s",
-          "traffic": None, "bytes_per_qp": bytes_qp,
-          "note": "HBM is touched only to load an instance and store its result; the %d loop passes per QP run in shared memory "
-                  "(latency/issue-bound, see profiles/)" % round(total_iter / B)}
-    rl["frac"] = rl["achieved"] / rl["peak"]
-    h2d = 8 * cnt * (nnzQ + nnzA + n + 2 * m)
-    d2h = cnt * (8 * (n + m) + 40 + m)
-    out = {"metric": METRIC, "value": B * args.steps / (worst[1] * 1e-3), "unit": "QP/s", "n_gpus": dist.world, "steps": args.steps,
-           "warmup": max(args.warmup, 3), "ms_per_step": worst[1] / args.steps, "higher_is_better": True, "scaling": "strong",
-           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": "c5: %d MPC QPs (n=%d, m=%d, nnzA=%d, common pattern), contiguous blocks over %d rank(s); "
-                                  "inputs %.0f MB per rank > 126 MB L2 (no flush needed)" % (B, n, m, nnzA, dist.world, h2d / 1e6),
-                      "batch": B, "n": n, "m": m, "nnzA": nnzA, "per_rank": cnt},
-           "kernel_ms_per_step": k_ms, "kernel_qp_per_s": B / (k_ms * 1e-3),
-           "batch_kernel": dict(info, mean_iterations=total_iter / B),
-           "result": {"solved": int((allsum["status_val"] == 1).sum()), "primal_infeasible": int((allsum["status_val"] == -3).sum()),
-                      "dual_infeasible": int((allsum["status_val"] == -4).sum()), "max_iter_reached": int((allsum["status_val"] == -2).sum()),
-                      "objective_sum": float(allsum["objective"][allsum["status_val"] == 1].sum()), "host_leg_matches_device_leg": same},
-           "roofline": rl,
-           "e2e": {"value": B * e2e_steps / (worst[2] * 1e-3), "unit": "QP/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                   "call": "qpdo_batch_solve (pinned host buffers in, x / y / summary / active set out)"},
-           "gpu_launches": args.steps, "clocks": clk.summary()}
-    bt.destroy()
-    return out
-
-
-def bench_reference(args, bounded=True):
-    """The reference's own CPU path for C5: the per-problem qpdo_setup / qpdo_solve / qpdo_cleanup loop
-    (oracle/ref_batch.c over oracle/_ref/libqpdo_ref.so) on all host cores, over a bounded sample
-    of the same instances."""
-    import oracle
-    from . import problems
-    ncores = os.cpu_count() or 1
-    sample = min(args.size or C5_BATCH, 2048 * max(1, ncores // 4))
-    b = problems.mpc_batch(sample)
-    n, m = b["n"], b["m"]
-    Qp = np.arange(n + 1); Qi = np.arange(n); Qx = np.tile(b["Qd"], (sample, 1))
-    if oracle.have_ref():
-        kind = "reference"
-        best = None
-        for _ in range(max(1, min(getattr(args, "steps", 1) or 1, 3))):
-            secs, summ = oracle.ref_batch_loop(n, m, Qp, Qi, b["Ap"], b["Ai"], Qx, b["Ax"], b["q"], b["l"], b["u"], threads=ncores)
-            best = secs if best is None else min(best, secs)
-        secs = best
-    else:
-        kind, ncores = "port", 1
-        sample = min(sample, 512)
-        t0 = time.perf_counter()
-        for i in range(sample):
-            oracle.solve(problems.mpc_instance(b, i), trace=False)
-        secs = time.perf_counter() - t0
-    return {"value": sample / secs, "unit": "QP/s", "cores": ncores, "kind": kind,
-            "sample": "first %d instances of the C5 batch, one qpdo_setup/qpdo_solve/qpdo_cleanup per QP, %d host thread(s)" % (sample, ncores),
-            "wall_s": secs}
-
-
-def smoke():
-    """a few MPC QPs through the batch C ABI on cuda:0, checked against the oracle"""
-    import oracle
-    from . import problems
-    B = 12
-    b = problems.mpc_batch(B, first=100)
-    bt, vals = from_mpc(b)
-    x, y, summ, act = bt.solve(*vals)
-    bt.destroy()
-    for i in range(B):
-        o = oracle.solve(problems.mpc_instance(b, i), trace=False)
-        ok = (int(summ[i]["status_val"]), int(summ[i]["iterations"]), int(summ[i]["oterations"])) == (o.status_val, o.iterations, o.oterations)
-        ok = ok and np.array_equal(act[i].astype(np.int8), o.active_set)
-        if o.status_val == 1:
-            ok = ok and np.abs(x[i] - o.x).max() <= 1e-8 * max(1.0, np.abs(o.x).max()) and np.abs(y[i] - o.y).max() <= 1e-8 * max(1.0, np.abs(o.y).max())
-        if not ok:
-            raise AssertionError("smoke(): batch kernel differs from the oracle on MPC instance %d" % i)
-    print("smoke batch: %d MPC QPs, statuses %s, iterations %s -> OK" % (B, list(summ["status_val"]), list(summ["iterations"])))
