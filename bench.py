@@ -235,6 +235,7 @@ from qpdo_b200 import batch as qbatch      # ctypes mirror of include/qpdo_batch
 import ctypes as C
 
 C5_BATCH = 65536
+TRAFFIC_PER_QP_NCU = 12062          # measured DRAM bytes per QP (26.55 MB read + 2.01 MB written for 2,368 QPs)
 
 
 def algorithmic_bytes_per_qp(n, m, nnzQ, nnzA):
@@ -327,7 +328,8 @@ def run_c5(args, dist):
     k_ms = worst[0] / args.steps
     rl = {"bound": "hbm", "kernel": "k_batch_solve (one CTA per QP, solver loop in shared memory)",
           "achieved": bytes_qp * cnt / (k_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s",
-          "traffic": None, "bytes_per_qp": bytes_qp,
+          "traffic": TRAFFIC_PER_QP_NCU * cnt, "traffic_source": "dram__bytes_read+write of one ncu --set full launch (profiles/r1_c5_batch.md), per QP x QPs per launch",
+          "bytes_per_qp": bytes_qp,
           "note": "HBM is touched only to load an instance and store its result; the %d loop passes per QP run in shared memory "
                   "(latency/issue-bound, see profiles/)" % round(total_iter / B)}
     rl["frac"] = rl["achieved"] / rl["peak"]
@@ -357,7 +359,7 @@ def ref_c5(args, bounded=True):
     import oracle
     from qpdo_b200 import problems
     ncores = os.cpu_count() or 1
-    sample = min(args.size or C5_BATCH, 2048 * max(1, ncores // 4))
+    sample = min(args.size or C5_BATCH, C5_BATCH)          # the whole batch: ~3 s on 16 cores per pass
     b = problems.mpc_batch(sample)
     n, m = b["n"], b["m"]
     Qp = np.arange(n + 1); Qi = np.arange(n); Qx = np.tile(b["Qd"], (sample, 1))
