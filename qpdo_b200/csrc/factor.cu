@@ -161,35 +161,38 @@ __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
         __syncthreads();
     }
 }
-// LDL' of the nb x nb diagonal block at (kb, kb): unit lower L11, D on the diagonal
-__global__ void __launch_bounds__(256) k_big_potrf(FArgs A, const int *list, int kb)
+// LDL' of the nb x nb diagonal block at (kb, kb): unit lower L11, D on the diagonal.  ONE warp per front,
+// lane = block row with its 32 entries in registers; the pivot and the scaled column travel by shuffle, so
+// the 32-pivot chain has no barrier and no shared-memory round trip (the chain, not the flops, is what a
+// lone CTA at the top of the tree pays for).  Per entry the fma sequence is ascending k, as everywhere.
+__global__ void __launch_bounds__(32) k_big_potrf(FArgs A, const int *list, int kb)
 {
-    __shared__ double D[NB][NB + 1];
     const int s = list[blockIdx.x];
     const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
     if (kb >= nc) return;
-    const int nb = min(NB, nc - kb), tid = threadIdx.x;
+    const int nb = min(NB, nc - kb), lane = threadIdx.x;
     double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N + kb;
-    for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; D[i][j] = Lb[(int64_t)j * N + i]; }
-    __syncthreads();
-    __shared__ double uc[NB], lc[NB];
-    for (int k = 0; k < nb; k++) {                  // two phases per pivot, as in k_front_smem
-        const double dk = D[k][k];
-        if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
-        if (tid > k && tid < nb) {
-            const double u = D[tid][k], l = div_by_pivot(u, dk, __drcp_rn(dk));
-            uc[tid] = u; lc[tid] = l; D[tid][k] = l;
+    double a[NB];
+#pragma unroll
+    for (int j = 0; j < NB; j++) a[j] = (j < nb && lane < nb && lane >= j) ? Lb[(int64_t)j * N + lane] : (lane == j ? 1.0 : 0.0);
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+        const double dk = __shfl_sync(0xffffffffu, a[k], k);
+        bad = bad || (k < nb && !(dk > 0.0));
+        const double ak = a[k];
+        const double l = div_by_pivot(ak, dk, __drcp_rn(dk));
+#pragma unroll
+        for (int j = k + 1; j < NB; j++) {
+            const double lj = __shfl_sync(0xffffffffu, l, j);
+            a[j] = fma(-ak, lj, a[j]);                   // rows above the diagonal carry garbage that is never stored
         }
-        __syncthreads();
-        const int R = nb - k - 1;
-        for (int idx = tid; idx < R * R; idx += 256) {
-            const int c = idx / R, r = idx - c * R;
-            if (r >= c) D[k + 1 + r][k + 1 + c] = fma(-uc[k + 1 + r], lc[k + 1 + c], D[k + 1 + r][k + 1 + c]);
-        }
-        __syncthreads();
+        if (lane > k) a[k] = l;
     }
-    __syncthreads();
-    for (int idx = tid; idx < nb * nb; idx += 256) { int j = idx / nb, i = idx - j * nb; Lb[(int64_t)j * N + i] = (i >= j) ? D[i][j] : 0.0; }
+    if (bad && lane == 0) A.sc->not_posdef = 1;
+#pragma unroll
+    for (int j = 0; j < NB; j++)
+        if (j < nb && lane < nb) Lb[(int64_t)j * N + lane] = (lane >= j) ? a[j] : 0.0;
 }
 // rows below the diagonal block: X <- X L11^{-T} D^{-1}, one row per thread
 __global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int kb)
@@ -278,6 +281,9 @@ __global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int 
 #pragma unroll
             for (int b = 0; b < 2; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
     }
+    // read-modify-write of the 16 destination entries: all loads first (one round trip), then the stores
+    double *dst[4][2][2];
+    double cur[4][2][2];
 #pragma unroll
     for (int a = 0; a < 4; a++)
 #pragma unroll
@@ -285,8 +291,16 @@ __global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int 
 #pragma unroll
             for (int e = 0; e < 2; e++) {
                 const int gi = ra + wr + a * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
-                if (gi < N && gj <= gi) { double *dst = front_elem(A, s, nc, nr, N, gi, gj); *dst -= acc[a][b][e]; }
+                dst[a][b][e] = (gi < N && gj <= gi) ? front_elem(A, s, nc, nr, N, gi, gj) : nullptr;
+                cur[a][b][e] = dst[a][b][e] ? *dst[a][b][e] : 0.0;
             }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                if (dst[a][b][e]) *dst[a][b][e] = cur[a][b][e] - acc[a][b][e];
 }
 
 // ------------------------------------------------------------------------------- triangular solves
@@ -514,7 +528,7 @@ static long issue_factor(qpdo_dev *d)
             if (L.kind == 2) {
                 k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, d->st>>>(A, list); launches++;
                 for (int kb = 0; kb < L.maxnc; kb += NB) {
-                    k_big_potrf<<<L.count, 256, 0, d->st>>>(A, list, kb); launches++;
+                    k_big_potrf<<<L.count, 32, 0, d->st>>>(A, list, kb); launches++;
                     int R = L.maxN - kb - 1;
                     if (R > 0) {
                         k_big_trsm<<<dim3(L.count, cdiv(R, 128)), 128, 0, d->st>>>(A, list, kb);
