@@ -81,36 +81,53 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
         }
         __syncthreads();
     }
-    // right-looking LDL', two phases per pivot: (A) the rows below the pivot compute l_i = a_ik / d_k into
-    // lcol (column k itself stays unscaled = L D while it updates), (B) the trailing lower triangle is
-    // dealt flat to all threads: a_ij = fma(-a_ik, l_j, a_ij).  Same fma sequence per entry as a
-    // column-by-column elimination.
-    double *lcol = F + (size_t)ld * N, *ucol = lcol + N;
-    for (int k = 0; k < nc; k++) {
-        const double dk = F[k + k * ld];
-        if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
-        const double rk = __drcp_rn(dk);
-        for (int i = k + 1 + tid; i < N; i += NT) {
-            const double u = F[i + k * ld], l = div_by_pivot(u, dk, rk);
-            ucol[i] = u; lcol[i] = l; F[i + k * ld] = l;
+    // right-looking LDL' in blocks of KB pivots.  Panel phase, per pivot: the rows below it compute
+    // l_i = a_ik / d_k (unscaled u_i and scaled l_i go to the ub / lb buffers, the L entry is final), then the
+    // remaining panel columns are updated.  Trailing phase, once per block: warp per column, lane per row
+    // (row values u_i^t stay in registers across the columns), a_ij = fma(-u^3, l^3, fma(... fma(-u^0, l^0, a_ij)))
+    // -- the same ascending-k fma sequence per entry as a column-by-column elimination, with a quarter of
+    // the shared-memory traffic and barriers.
+    constexpr int KB = 4, RMAX = 5;                        // fronts up to 32 * RMAX = 160 rows
+    const int lane = tid & 31, wid = tid >> 5, NW = NT / 32;
+    double *ub = F + (size_t)ld * N, *lb = ub + KB * N;
+    for (int kb = 0; kb < nc; kb += KB) {
+        const int nk = min(KB, nc - kb);
+        for (int t = 0; t < nk; t++) {
+            const int k = kb + t;
+            const double dk = F[k + k * ld];
+            if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
+            const double rk = __drcp_rn(dk);
+            for (int i = k + 1 + tid; i < N; i += NT) {
+                const double u = F[i + k * ld], l = div_by_pivot(u, dk, rk);
+                ub[t * N + i] = u; lb[t * N + i] = l; F[i + k * ld] = l;
+            }
+            __syncthreads();
+            if (t + 1 < nk) {
+                for (int c = k + 1; c < kb + nk; c++) {
+                    const double lc = lb[t * N + c];
+                    for (int i = c + tid; i < N; i += NT) F[i + c * ld] = fma(-ub[t * N + i], lc, F[i + c * ld]);
+                }
+                __syncthreads();
+            }
         }
-        __syncthreads();
-        const int R = N - k - 1;                           // trailing order; columns j = k+1+jj, rows i = j..N-1
-        for (int jj = 0; jj < R; jj++) {
-            // column jj has R - jj entries; short columns are batched below
-            if (R - jj < NT / 2) break;
-            const int j = k + 1 + jj;
-            const double lj = lcol[j];
-            for (int i = j + tid; i < N; i += NT) F[i + j * ld] = fma(-ucol[i], lj, F[i + j * ld]);
-        }
-        {   // remaining short columns: flat index over the (rows x columns) rectangle, upper part skipped
-            int jj0 = 0;
-            while (jj0 < R && R - jj0 >= NT / 2) jj0++;
-            const int C = R - jj0, H = R - jj0;              // C columns, the tallest has H entries
-            for (int idx = tid; idx < C * H; idx += NT) {
-                const int c = idx / H, r = idx - c * H;
-                const int j = k + 1 + jj0 + c, i = j + r;
-                if (i < N) F[i + j * ld] = fma(-ucol[i], lcol[j], F[i + j * ld]);
+        double ur[RMAX][KB];
+#pragma unroll
+        for (int r = 0; r < RMAX; r++)
+#pragma unroll
+            for (int t = 0; t < KB; t++) { const int i = lane + 32 * r; ur[r][t] = (t < nk && i < N) ? ub[t * N + i] : 0.0; }
+        for (int j = kb + nk + wid; j < N; j += NW) {
+            double lj[KB];
+#pragma unroll
+            for (int t = 0; t < KB; t++) lj[t] = (t < nk) ? lb[t * N + j] : 0.0;
+#pragma unroll
+            for (int r = 0; r < RMAX; r++) {
+                const int i = lane + 32 * r;
+                if (i >= j && i < N) {
+                    double v = F[i + j * ld];
+#pragma unroll
+                    for (int t = 0; t < KB; t++) if (t < nk) v = fma(-ur[r][t], lj[t], v);
+                    F[i + j * ld] = v;
+                }
             }
         }
         __syncthreads();
@@ -149,13 +166,20 @@ __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
         const double *U = A.Ux + A.Up[c];
         int lo = 0, hi = rc;                       // first jj with rl[jj] >= c0
         while (lo < hi) { int mid = (lo + hi) >> 1; if (rl[mid] < c0) lo = mid + 1; else hi = mid; }
-        for (int jj = lo; jj < rc; jj++) {
+        // one warp per source column, 8 independent read-modify-writes in flight per lane (the extend-add
+        // is a chain of dependent global accesses: index -> address -> load -> store)
+        for (int jj = lo + (tid >> 5); jj < rc; jj += 8) {
             const int dc = rl[jj];
             if (dc >= c1) break;
             const double *ucol = U + (int64_t)jj * rc;
-            for (int ii = jj + tid; ii < rc; ii += 256) {
-                double *dst = front_elem(A, s, nc, nr, N, rl[ii], dc);
-                *dst += ucol[ii];
+            for (int ii0 = jj + (tid & 31); ii0 < rc; ii0 += 32 * 8) {
+                int r[8]; double v[8], cur[8]; double *dst[8];
+#pragma unroll
+                for (int t = 0; t < 8; t++) { const int ii = ii0 + 32 * t; const bool ok = ii < rc; r[t] = ok ? rl[ii] : -1; v[t] = ok ? ucol[ii] : 0.0; }
+#pragma unroll
+                for (int t = 0; t < 8; t++) { dst[t] = r[t] >= 0 ? front_elem(A, s, nc, nr, N, r[t], dc) : nullptr; cur[t] = dst[t] ? *dst[t] : 0.0; }
+#pragma unroll
+                for (int t = 0; t < 8; t++) if (dst[t]) *dst[t] = cur[t] + v[t];
             }
         }
         __syncthreads();
@@ -538,7 +562,7 @@ static long issue_factor(qpdo_dev *d)
                     }
                 }
             } else {
-                size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 2 * (size_t)L.maxN);
+                size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 8 * (size_t)L.maxN);
                 if (L.maxnc == 0) k_front_smem<64><<<L.count, 64, smem, d->st>>>(A, list);
                 else if (L.maxnc == 1) k_front_smem<128><<<L.count, 128, smem, d->st>>>(A, list);
                 else k_front_smem<256><<<L.count, 256, smem, d->st>>>(A, list);
