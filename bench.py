@@ -147,10 +147,10 @@ def run_c3(args, dist):
     t0 = time.time()
     s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], st)
     setup_s = time.time() - t0
-    info = capi.DevSymbolicInfo()
-    lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, 1)):
         r = s.solve()
+    info = capi.DevSymbolicInfo()                      # after a solve: large problems analyse lazily (pattern management)
+    lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
     prof = capi.DevProfile()
     lib.qpdo_dev_set_profiling(s.device, 1)
     lib.qpdo_dev_get_profile(s.device, C.byref(prof), 1)

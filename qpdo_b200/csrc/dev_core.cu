@@ -305,9 +305,7 @@ extern "C" int qpdo_dev_create(qpdo_dev **out, const qpdo_dev_problem *p, int sc
         if (cudaMallocHost((void **)&d->sc_host, sizeof(qpdo_dev_scalars)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); break; }
         memset(d->sc_host, 0, sizeof(qpdo_dev_scalars));
         // symbolic analysis on the host (pattern only, independent of the scaling)
-        auto t0 = std::chrono::steady_clock::now();
-        if (factor_setup(d, ordering)) break;
-        d->analyze_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (factor_setup(d, ordering)) break;            // accumulates d->analyze_seconds
         if (linesearch_setup(d)) break;
         if (scaling_iters > 0) { if (run_scaling(d, scaling_iters)) break; }
         else {
@@ -356,6 +354,7 @@ extern "C" int qpdo_dev_get_scaling(qpdo_dev *d, double *D, double *Dinv, double
 extern "C" int qpdo_dev_get_symbolic_info(qpdo_dev *d, qpdo_dev_symbolic_info *o)
 {
     const qpdo_symbolic *S = d->F.S;
+    if (!S) { memset(o, 0, sizeof *o); o->analyze_seconds = d->analyze_seconds; return 0; }      // dynamic pattern, nothing factored yet
     o->nsuper = S->nsuper; o->nlevel = S->nlevel; o->max_front = S->max_front; o->max_nc = S->max_nc;
     o->lnz = S->lnz; o->lnz_stored = S->lnz_stored; o->usize = S->usize; o->nnzK = S->nnzK; o->ntriple = S->ntriple;
     o->flops = S->flops; o->analyze_seconds = d->analyze_seconds;

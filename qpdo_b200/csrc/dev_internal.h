@@ -45,6 +45,13 @@ struct Factor {
     std::vector<std::vector<FrontLaunch>> plan;   // per level
     cudaGraphExec_t g_factor = nullptr, g_solve = nullptr;
     long launches_factor = 0, launches_solve = 0;
+    // pattern management (factor.cu): row set P of A that the current symbolic structure covers
+    std::vector<int> hQp, hQi, hAp, hAi;          // host copies of the patterns
+    std::vector<void *> owned;                    // device arrays that depend on the pattern
+    unsigned char *inP = nullptr;                 // [m] row is in P
+    int *cnt = nullptr, *cnt_host = nullptr;      // support / outside counters
+    int ordering = 1, npattern = 0, analyses = 0;
+    bool dynamic = false, full = false;
 };
 
 struct qpdo_dev {

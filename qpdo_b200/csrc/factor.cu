@@ -13,6 +13,9 @@
 // The whole sequence is captured once into a CUDA graph and replayed every Newton step.
 #include "dev_internal.h"
 #include <algorithm>
+#include <chrono>
+#include <stdlib.h>
+#include <string.h>
 
 #define NB 32          // panel width of the blocked path
 #define CW 32          // destination-column chunk of the big-front assembly
@@ -471,37 +474,118 @@ static SArgs sargs(qpdo_dev *d)
     return A;
 }
 
+// ---- pattern management ---------------------------------------------------------------------------
+// K = Q + sigma I + A' diag(omega) A is factored on the pattern of Q plus the rows of A in a ROW SET P that
+// covers the support of omega.  P = all rows (the fixed superset, one analysis for the whole solve) is the
+// default; for large problems whose support is a small fraction of m (Lasso paths: a handful of active rows
+// out of 100,000) the superset factor is orders of magnitude more work than the reference's, which
+// re-analyses on the active pattern at every refactor (cholmod_interface.c:10).  There P follows the
+// support: a counting kernel checks support(omega) <= P before every factorization, and the host
+// re-analyses (60 ms for n = 200k) only when a row outside P gains weight.
+static const int DYNAMIC_MIN_ROWS = 20000;                // smaller problems always use the superset
+static const int FULL_FRACTION = 8;                       // support > m / FULL_FRACTION: superset from then on
+
+template <class T> static int f_alloc(qpdo_dev *d, T **p, size_t count) { if (dev_alloc(d, p, count)) return -1; d->F.owned.push_back((void *)*p); return 0; }
+template <class T> static int f_upload(qpdo_dev *d, T **p, const T *h, size_t count) { if (dev_upload(d, p, h, count)) return -1; d->F.owned.push_back((void *)*p); return 0; }
+static void factor_release(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    cudaStreamSynchronize(d->st);
+    if (F.g_factor) cudaGraphExecDestroy(F.g_factor);
+    if (F.g_solve) cudaGraphExecDestroy(F.g_solve);
+    F.g_factor = F.g_solve = nullptr;
+    for (void *q : F.owned) {
+        for (size_t i = 0; i < d->allocs.size(); i++) if (d->allocs[i] == q) { d->allocs[i] = d->allocs.back(); d->allocs.pop_back(); break; }
+        cudaFree(q);
+    }
+    F.owned.clear();
+    if (F.S) qpdo_symbolic_free(F.S);
+    F.S = nullptr;
+}
+
+__global__ void k_support(const double *omega, const unsigned char *inP, int m, int *cnt)
+{   // cnt[0] = rows carrying weight, cnt[1] = those outside the current pattern row set
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool sup = i < m && omega[i] != 0.0, out = sup && !inP[i];
+    const unsigned bs = __ballot_sync(0xffffffffu, sup), bo = __ballot_sync(0xffffffffu, out);
+    if ((threadIdx.x & 31) == 0) { if (bs) atomicAdd(&cnt[0], __popc(bs)); if (bo) atomicAdd(&cnt[1], __popc(bo)); }
+}
+
+static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask);
+
 int factor_setup(qpdo_dev *d, int ordering)
 {
     Factor &F = d->F;
     const int n = d->n, m = d->m;
-    // pull the patterns back from the problem that dev_core uploaded: simpler to re-read host copies
-    std::vector<int> Qp(n + 1), Qi(d->nnzQ ? d->nnzQ : 1), Ap(n + 1), Ai(d->nnzA ? d->nnzA : 1);
-    CUDA_OK(cudaMemcpyAsync(Qp.data(), d->Qp, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
-    CUDA_OK(cudaMemcpyAsync(Ap.data(), d->Ap, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
-    if (d->nnzQ) CUDA_OK(cudaMemcpyAsync(Qi.data(), d->Qi, sizeof(int) * d->nnzQ, cudaMemcpyDeviceToHost, d->st));
-    if (d->nnzA) CUDA_OK(cudaMemcpyAsync(Ai.data(), d->Ai, sizeof(int) * d->nnzA, cudaMemcpyDeviceToHost, d->st));
+    F.ordering = ordering;
+    // host copies of the patterns (re-analysis needs them)
+    F.hQp.assign(n + 1, 0); F.hQi.assign(d->nnzQ ? d->nnzQ : 1, 0); F.hAp.assign(n + 1, 0); F.hAi.assign(d->nnzA ? d->nnzA : 1, 0);
+    CUDA_OK(cudaMemcpyAsync(F.hQp.data(), d->Qp, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaMemcpyAsync(F.hAp.data(), d->Ap, sizeof(int) * (n + 1), cudaMemcpyDeviceToHost, d->st));
+    if (d->nnzQ) CUDA_OK(cudaMemcpyAsync(F.hQi.data(), d->Qi, sizeof(int) * d->nnzQ, cudaMemcpyDeviceToHost, d->st));
+    if (d->nnzA) CUDA_OK(cudaMemcpyAsync(F.hAi.data(), d->Ai, sizeof(int) * d->nnzA, cudaMemcpyDeviceToHost, d->st));
     CUDA_OK(cudaStreamSynchronize(d->st));
+    if (dev_alloc(d, &F.xs, n) || dev_alloc(d, &F.inP, (size_t)std::max(m, 1)) || dev_alloc(d, &F.cnt, 2)) return -1;
+    if (cudaMallocHost((void **)&F.cnt_host, 2 * sizeof(int)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); return -1; }
+    cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const char *ev = getenv("QPDO_PATTERN");              // "superset" | "dynamic" override the size rule (tests)
+    F.dynamic = (m >= DYNAMIC_MIN_ROWS);
+    if (ev && !strcmp(ev, "superset")) F.dynamic = false;
+    if (ev && !strcmp(ev, "dynamic") && m > 0) F.dynamic = true;
+    if (!F.dynamic) return factor_analyze(d, nullptr);    // superset, once, at setup
+    return 0;                                             // dynamic: first analysis at the first factorization
+}
+
+// analyse on pattern(Q) + rows of A selected by rowmask (nullptr: all rows) and rebuild the device structures
+static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
+{
+    Factor &F = d->F;
+    const int n = d->n, m = d->m;
+    auto t0 = std::chrono::steady_clock::now();
+    factor_release(d);
+    std::vector<int> Ap, Ai, rowmap, nzmap;
+    const int *pAp = F.hAp.data(), *pAi = F.hAi.data();
+    int mr = m;
+    std::vector<unsigned char> inP((size_t)std::max(m, 1), rowmask ? 0 : 1);
+    if (rowmask) {
+        std::vector<int> newid(m, -1);
+        mr = 0;
+        for (int i = 0; i < m; i++) if (rowmask[i]) { newid[i] = mr++; rowmap.push_back(i); inP[i] = 1; }
+        Ap.assign(n + 1, 0);
+        for (int j = 0; j < n; j++) {
+            for (int t = F.hAp[j]; t < F.hAp[j + 1]; t++) if (newid[F.hAi[t]] >= 0) { Ai.push_back(newid[F.hAi[t]]); nzmap.push_back(t); }
+            Ap[j + 1] = (int)Ai.size();
+        }
+        if (Ai.empty()) Ai.push_back(0);
+        pAp = Ap.data(); pAi = Ai.data();
+    }
+    F.full = (rowmask == nullptr); F.npattern = mr;
     char err[256];
-    qpdo_symbolic *S = qpdo_symbolic_analyze(n, m, Qp.data(), Qi.data(), Ap.data(), Ai.data(), ordering, err);
+    qpdo_symbolic *S = qpdo_symbolic_analyze(n, mr, F.hQp.data(), F.hQi.data(), pAp, pAi, F.ordering, err);
     if (!S) { qpdo_set_error("symbolic analysis failed: %s", err); return -1; }
+    if (rowmask) {                                        // back to the numbering of the full A
+        for (int64_t t = 0; t < S->ntriple; t++) { S->Kt_row[t] = rowmap[S->Kt_row[t]]; S->Kt_a1[t] = nzmap[S->Kt_a1[t]]; S->Kt_a2[t] = nzmap[S->Kt_a2[t]]; }
+    }
     F.S = S;
+    F.analyses++;
+    if (m) CUDA_OK(cudaMemcpyAsync(F.inP, inP.data(), (size_t)m, cudaMemcpyHostToDevice, d->st));
     const int ns = S->nsuper;
     const int64_t nrows = S->sn_rowptr[ns];
     std::vector<int> Kcol(S->nnzK);
     for (int k = 0; k < n; k++) for (int e = S->Kp[k]; e < S->Kp[k + 1]; e++) Kcol[e] = k;
-    if (dev_upload(d, &F.sn_start, S->sn_start, ns + 1) || dev_upload(d, &F.sn_nr, S->sn_nr, ns) ||
-        dev_upload(d, &F.rows, S->rows, nrows) || dev_upload(d, &F.rel, S->rel, nrows) ||
-        dev_upload(d, &F.child_ptr, S->child_ptr, ns + 1) || dev_upload(d, &F.child_idx, S->child_idx, ns) ||
-        dev_upload(d, &F.level_sn, S->level_sn, ns) || dev_upload(d, &F.sn_rowptr, S->sn_rowptr, ns + 1) ||
-        dev_upload(d, &F.Lp, S->Lp, ns + 1) || dev_upload(d, &F.Up, S->Up, ns + 1) ||
-        dev_upload(d, &F.perm, S->perm, n) || dev_upload(d, &F.pinv, S->pinv, n) ||
-        dev_upload(d, &F.Ki, S->Ki, S->nnzK) || dev_upload(d, &F.Kcol, Kcol.data(), S->nnzK) ||
-        dev_upload(d, &F.Kq, S->Kq, S->nnzK) || dev_upload(d, &F.Kdst, S->Kdst, S->nnzK) ||
-        dev_upload(d, &F.Ktp, S->Ktp, S->nnzK + 1) || dev_upload(d, &F.Kt_row, S->Kt_row, S->ntriple) ||
-        dev_upload(d, &F.Kt_a1, S->Kt_a1, S->ntriple) || dev_upload(d, &F.Kt_a2, S->Kt_a2, S->ntriple) ||
-        dev_alloc(d, &F.Kt_val, S->ntriple) || dev_alloc(d, &F.Lx, S->lnz_stored) || dev_alloc(d, &F.Ux, S->usize) ||
-        dev_alloc(d, &F.xs, n) || dev_alloc(d, &F.uv, nrows))
+    if (f_upload(d, &F.sn_start, (const int *)S->sn_start, ns + 1) || f_upload(d, &F.sn_nr, (const int *)S->sn_nr, ns) ||
+        f_upload(d, &F.rows, (const int *)S->rows, nrows) || f_upload(d, &F.rel, (const int *)S->rel, nrows) ||
+        f_upload(d, &F.child_ptr, (const int *)S->child_ptr, ns + 1) || f_upload(d, &F.child_idx, (const int *)S->child_idx, ns) ||
+        f_upload(d, &F.level_sn, (const int *)S->level_sn, ns) || f_upload(d, &F.sn_rowptr, (const int64_t *)S->sn_rowptr, ns + 1) ||
+        f_upload(d, &F.Lp, (const int64_t *)S->Lp, ns + 1) || f_upload(d, &F.Up, (const int64_t *)S->Up, ns + 1) ||
+        f_upload(d, &F.perm, (const int *)S->perm, n) || f_upload(d, &F.pinv, (const int *)S->pinv, n) ||
+        f_upload(d, &F.Ki, (const int *)S->Ki, S->nnzK) || f_upload(d, &F.Kcol, (const int *)Kcol.data(), S->nnzK) ||
+        f_upload(d, &F.Kq, (const int *)S->Kq, S->nnzK) || f_upload(d, &F.Kdst, (const int64_t *)S->Kdst, S->nnzK) ||
+        f_upload(d, &F.Ktp, (const int64_t *)S->Ktp, S->nnzK + 1) || f_upload(d, &F.Kt_row, (const int *)S->Kt_row, S->ntriple) ||
+        f_upload(d, &F.Kt_a1, (const int *)S->Kt_a1, S->ntriple) || f_upload(d, &F.Kt_a2, (const int *)S->Kt_a2, S->ntriple) ||
+        f_alloc(d, &F.Kt_val, S->ntriple) || f_alloc(d, &F.Lx, S->lnz_stored) || f_alloc(d, &F.Ux, S->usize) ||
+        f_alloc(d, &F.uv, nrows))
         return -1;
     // launch plan: per level, fronts are sorted by decreasing order N
     F.plan.assign(S->nlevel, std::vector<FrontLaunch>());
@@ -528,14 +612,35 @@ int factor_setup(qpdo_dev *d, int ordering)
             }
         }
     }
-    cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    return 0;
+    d->analyze_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return factor_refresh_products(d);
+}
+
+// before a factorization: does the pattern row set still cover the support of omega?
+static int factor_ensure_pattern(qpdo_dev *d)
+{
+    Factor &F = d->F;
+    const int m = d->m;
+    if (F.S && (F.full || !F.dynamic)) return 0;
+    CUDA_OK(cudaMemsetAsync(F.cnt, 0, 2 * sizeof(int), d->st));
+    if (m) k_support<<<cdiv(m, 256), 256, 0, d->st>>>(d->omega, F.inP, m, F.cnt);
+    CUDA_OK(cudaMemcpyAsync(F.cnt_host, F.cnt, 2 * sizeof(int), cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaStreamSynchronize(d->st));
+    const int support = F.cnt_host[0], outside = F.cnt_host[1];
+    if (F.S && outside == 0 && F.npattern <= 4 * support + 4096) return 0;
+    if ((long)support * FULL_FRACTION > (long)m) return factor_analyze(d, nullptr);
+    std::vector<double> om((size_t)m);
+    CUDA_OK(cudaMemcpyAsync(om.data(), d->omega, sizeof(double) * m, cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaStreamSynchronize(d->st));
+    std::vector<unsigned char> mask((size_t)m);
+    for (int i = 0; i < m; i++) mask[i] = om[i] != 0.0;
+    return factor_analyze(d, mask.data());
 }
 
 int factor_refresh_products(qpdo_dev *d)
 {
     Factor &F = d->F;
+    if (!F.S) return 0;                                   // dynamic pattern: nothing analysed yet
     if (F.S->ntriple) k_products<<<cdiv(F.S->ntriple, 256), 256, 0, d->st>>>(F.S->ntriple, F.Kt_a1, F.Kt_a2, d->Ax, F.Kt_val);
     return 0;
 }
@@ -624,6 +729,7 @@ static int capture(qpdo_dev *d, long (*issue)(qpdo_dev *), cudaGraphExec_t *out,
 int factor_numeric(qpdo_dev *d)
 {
     Factor &F = d->F;
+    if (factor_ensure_pattern(d)) return -1;
     const qpdo_symbolic *S = F.S;
     {
         PhaseTimer t(d, PH_ASSEMBLE);
@@ -656,9 +762,7 @@ int factor_solve(qpdo_dev *d, const double *rhs, double *x)
 void factor_destroy(qpdo_dev *d)
 {
     Factor &F = d->F;
-    if (F.g_factor) cudaGraphExecDestroy(F.g_factor);
-    if (F.g_solve) cudaGraphExecDestroy(F.g_solve);
-    F.g_factor = F.g_solve = nullptr;
-    if (F.S) qpdo_symbolic_free(F.S);
-    F.S = nullptr;
+    factor_release(d);
+    if (F.cnt_host) cudaFreeHost(F.cnt_host);
+    F.cnt_host = nullptr;
 }

@@ -9,7 +9,7 @@ import oracle
 from qpdo_b200 import capi, problems
 
 
-def run(name, p, st, path=False):
+def run(name, p, st, path=False, stride=1):
     ref = oracle.ref_library()
     s = capi.Solver(ref)
     t0 = time.time()
@@ -37,6 +37,11 @@ def run(name, p, st, path=False):
             xs, ys = rj.x, rj.y
     s.delete()
     out["total_seconds"] = time.time() - t0
+    if stride > 1:                      # keep the fixture small: every stride-th entry of the solution vectors
+        for k in ("x", "y", "pathlast_x", "pathlast_y"):
+            if k in out:
+                out[k] = out[k][::stride]
+        out["stride"] = stride
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
@@ -47,6 +52,6 @@ if __name__ == "__main__":
     elif which == "cont120":
         run("cont120", problems.cont_like(120), {})
     elif which == "lasso":
-        run("lasso_c4", problems.lasso_dual(), {}, path=True)
+        run("lasso_c4", problems.lasso_dual(), {}, path=True, stride=16)
     elif which == "lasso_mid":
         run("lasso_mid", problems.lasso_dual(20000, 10000, window=200, npath=6), {}, path=True)

@@ -192,3 +192,54 @@ def test_full_size_cont300_against_reference_golden(cuda_lib):
     Ax = A @ r.x
     assert np.abs(Ax - np.clip(Ax + r.y, p["l"], p["u"])).max() <= 1e-5
     assert np.abs(Q @ r.x + p["q"] + A.T @ r.y).max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", ["lasso_small", "rand300", "cont40", "mpc0", "c1"])
+def test_dynamic_pattern_matches_golden_and_superset(name, monkeypatch):
+    """pattern management (factor.cu): the row set of A behind the symbolic structure follows the support of
+    omega (re-analysis on demand, what the reference does at every refactor, cholmod_interface.c:10) or is
+    the fixed superset; both must reproduce the reference's cold solve"""
+    gen, st = CASES[name]
+    p = gen()
+    g = load_golden(name)
+    res = {}
+    for mode in ("superset", "dynamic"):
+        monkeypatch.setenv("QPDO_PATTERN", mode)
+        res[mode] = gpu_solve(p, st)
+        check("%s[%s]" % (name, mode), g, res[mode], "cold_", exact_iters=name not in KNIFE_EDGE)
+    a, b = res["superset"], res["dynamic"]
+    assert (a.status_val, a.iterations, a.oterations) == (b.status_val, b.iterations, b.oterations)
+    assert np.array_equal(a.active_set, b.active_set)
+    assert rel_err(a.x, b.x) <= 1e-9 and rel_err(a.y, b.y) <= 1e-9
+
+
+def test_full_size_lasso_path_against_reference_golden():
+    """BASELINE config 4 at full size (n = 200,000, m = 100,000): the whole 20-step regularisation path
+    (qpdo_update_bounds + qpdo_warm_start + qpdo_solve per step) against the unmodified reference
+    (tests/golden/lasso_c4.npz, make_golden_large.py lasso; x, y stored with a stride)."""
+    p = problems.lasso_dual()
+    g = load_golden("lasso_c4")
+    stride = int(g["stride"])
+    m = p["A"].shape[0]
+    s = gpu_solver()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+    r = s.solve()
+    assert (r.status_val, r.iterations, r.oterations) == (int(g["status_val"]), int(g["iterations"]), int(g["oterations"]))
+    assert np.array_equal(np.packbits(r.active_set.astype(np.uint8)), g["active_set"])
+    assert rel_err(g["x"], r.x[::stride]) <= TOL and rel_err(g["y"], r.y[::stride]) <= TOL
+    assert abs(r.objective - float(g["objective"])) <= TOL * max(1.0, abs(float(g["objective"])))
+    x, y = r.x.copy(), r.y.copy()
+    last = len(p["lams"]) - 1
+    for j, lam in enumerate(p["lams"][1:], 1):
+        s.update_bounds(np.full(m, -lam), np.full(m, lam))
+        s.warm_start(x, y)
+        r = s.solve()
+        tag = "path %d" % j
+        assert (r.status_val, r.iterations, r.oterations) == (int(g["path%d_status_val" % j]), int(g["path%d_iterations" % j]),
+                                                              int(g["path%d_oterations" % j])), tag
+        assert np.array_equal(np.packbits(r.active_set.astype(np.uint8)), g["path%d_active_set" % j]), tag
+        assert abs(r.objective - float(g["path%d_objective" % j])) <= TOL * max(1.0, abs(float(g["path%d_objective" % j]))), tag
+        x, y = r.x.copy(), r.y.copy()
+        if j == last:
+            assert rel_err(g["pathlast_x"], x[::stride]) <= TOL and rel_err(g["pathlast_y"], y[::stride]) <= TOL
+    s.delete()

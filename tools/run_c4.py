@@ -20,10 +20,6 @@ t0 = time.time()
 s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
 print("setup %.2f s" % (time.time() - t0), flush=True)
 lib = qpdo_b200.lib()
-info = capi.DevSymbolicInfo()
-lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
-print("symbolic: nsuper %d nlevel %d max_front %d lnz %.3g flops %.3g analyze %.2f s" %
-      (info.nsuper, info.nlevel, info.max_front, info.lnz, info.flops, info.analyze_seconds), flush=True)
 x = y = None
 A = p["A"].tocsr()
 for j, lam in enumerate(p["lams"][:npath]):
@@ -42,5 +38,9 @@ for j, lam in enumerate(p["lams"][:npath]):
     print("path %2d lam %.4g: status %d iter %d/%d obj %.10g  %.2f s  | dual res %.2e prim viol %.2e compl %.2e nnz(y) %d" %
           (j, lam, r.status_val, r.iterations, r.oterations, r.objective, dt, rd, rp, comp, int((np.abs(y) > 1e-9).sum())), flush=True)
     assert r.status_val == 1 and rd < 1e-4 and rp < 1e-4
+    info = capi.DevSymbolicInfo()
+    lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
+    print("        symbolic now: nsuper %d nlevel %d max_front %d lnz %.3g flops %.3g, analysis total %.2f s" %
+          (info.nsuper, info.nlevel, info.max_front, info.lnz, info.flops, info.analyze_seconds), flush=True)
 s.delete()
 print("C4_OK")
