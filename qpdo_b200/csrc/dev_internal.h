@@ -38,7 +38,8 @@ struct Factor {
     int *Kcol = nullptr;             // column of each K entry (diagonal test)
     int64_t *Kdst = nullptr, *Ktp = nullptr;
     double *Kt_val = nullptr;        // a_ir * a_ic per triple (recomputed when A is rescaled)
-    double *Lx = nullptr;            // L panels
+    double *Lx = nullptr;            // L panels (working values; final for the smem fronts)
+    double *Xout = nullptr;          // final L panels of the big (blocked) fronts
     double *Ux = nullptr;            // update matrices
     double *xs = nullptr;            // permuted rhs / solution
     double *uv = nullptr;            // per-front update vectors of the forward solve

@@ -26,6 +26,7 @@ struct FArgs {
     const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
     const int64_t *sn_rowptr, *Lp, *Up;
     double *Lx, *Ux;
+    double *Xout;              // final L panels of the big (blocked) fronts; Lx keeps their working values
     qpdo_dev_scalars *sc;
 };
 
@@ -330,11 +331,141 @@ __global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int 
                 if (dst[a][b][e]) *dst[a][b][e] = cur[a][b][e] - acc[a][b][e];
 }
 
+// One launch per 32-pivot panel step of a big front: every CTA (front, tile pair) redoes the LDL' of the
+// diagonal block (one warp, registers) and the triangular solve of ITS two 64-row tiles from the raw panel,
+// then applies the rank-32 update of its 64 x 64 tile on the FP64 tensor pipe.  The factored panel goes to
+// Xout (tile pairs with tj == 0 write their rows, pair 0 the diagonal block), the raw panel in Lx stays
+// intact for the other CTAs -- so potrf -> trsm -> syrk needs no grid-wide ordering, and the serial chain of
+// the tree top pays one launch per panel instead of three.  Arithmetic identical to the three-kernel path.
+__global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int kb)
+{
+    __shared__ double Pa[TS * PLD], Pb[TS * PLD];
+    __shared__ double D[NB][NB + 1];
+    __shared__ double Rinv[NB];
+    const int s = list[blockIdx.x];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    if (kb >= nc) return;
+    const int nb = min(NB, nc - kb);
+    const int r0 = kb + nb, R = N - r0;
+    const int nt = (R + TS - 1) / TS;
+    int ti = (int)((sqrt(8.0 * blockIdx.y + 1.0) - 1.0) * 0.5);
+    while ((ti + 1) * (ti + 2) / 2 <= (int)blockIdx.y) ti++;
+    while (ti * (ti + 1) / 2 > (int)blockIdx.y) ti--;
+    const int tj = blockIdx.y - ti * (ti + 1) / 2;
+    if (blockIdx.y > 0 && ti >= nt) return;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const double *Lraw = A.Lx + A.Lp[s] + (int64_t)kb * N;          // raw panel, column k at Lraw + k * N
+    double *Xo = A.Xout + A.Lp[s] + (int64_t)kb * N;
+    // ---- LDL' of the diagonal block (warp 0), result in D: unit lower L11, D on the diagonal
+    if (wid == 0) {
+        double a[NB];
+#pragma unroll
+        for (int j = 0; j < NB; j++) a[j] = (j < nb && lane < nb && lane >= j) ? Lraw[(int64_t)j * N + kb + lane] : (lane == j ? 1.0 : 0.0);
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < NB; k++) {
+            const double dk = __shfl_sync(0xffffffffu, a[k], k);
+            bad = bad || (k < nb && !(dk > 0.0));
+            const double ak = a[k];
+            const double l = div_by_pivot(ak, dk, __drcp_rn(dk));
+#pragma unroll
+            for (int j = k + 1; j < NB; j++) {
+                const double lj = __shfl_sync(0xffffffffu, l, j);
+                a[j] = fma(-ak, lj, a[j]);
+            }
+            if (lane > k) a[k] = l;
+        }
+        if (bad && lane == 0 && blockIdx.y == 0) A.sc->not_posdef = 1;
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            D[lane][j] = (lane >= j) ? a[j] : 0.0;
+            if (blockIdx.y == 0 && j < nb && lane < nb) Xo[(int64_t)j * N + kb + lane] = (lane >= j) ? a[j] : 0.0;
+        }
+        __syncwarp();
+        Rinv[lane] = __drcp_rn(D[lane][lane]);
+    }
+    __syncthreads();
+    if (R <= 0) return;
+    // ---- triangular solve of the two row tiles: thread t < 64 owns row ra + t, thread 64 + t row rb + t
+    const int ra = r0 + ti * TS, rb = r0 + tj * TS;
+    if (tid < 2 * TS) {
+        const bool second = tid >= TS;
+        const int r = second ? tid - TS : tid, i = (second ? rb : ra) + r;
+        double x[NB];
+        const bool live = i < N && !(second && ti == tj);
+#pragma unroll
+        for (int j = 0; j < NB; j++) x[j] = (live && j < nb) ? Lraw[(int64_t)j * N + i] : 0.0;
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            double v = x[j];
+#pragma unroll
+            for (int k = 0; k < j; k++) v = fma(-x[k], D[j][k], v);
+            x[j] = v;
+        }
+#pragma unroll
+        for (int j = 0; j < NB; j++) x[j] = div_by_pivot(x[j], D[j][j], Rinv[j]);
+        double *P = second ? Pb : Pa;
+        if (!(second && ti == tj)) {
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
+                const double xv = (j < nb && i < N) ? x[j] : 0.0;
+                if (!second) { Pa[r * PLD + j] = xv * D[j][j]; if (ti == tj) Pb[r * PLD + j] = xv; }
+                else P[r * PLD + j] = xv;
+            }
+            if (!second && tj == 0 && i < N) {
+#pragma unroll
+                for (int j = 0; j < NB; j++) if (j < nb) Xo[(int64_t)j * N + i] = x[j];
+            }
+        }
+    }
+    __syncthreads();
+    // ---- rank-nb update of the 64 x 64 tile (ti, tj): C -= (X D) X'
+    const int wr = (wid & 1) * 32, wc = (wid >> 1) * 16;
+    const int g = lane >> 2, q = lane & 3;
+    double acc[4][2][2];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ks++) {
+        double af[4], bf[2];
+#pragma unroll
+        for (int a = 0; a < 4; a++) af[a] = Pa[(wr + a * 8 + g) * PLD + ks * 4 + q];
+#pragma unroll
+        for (int b = 0; b < 2; b++) bf[b] = Pb[(wc + b * 8 + g) * PLD + ks * 4 + q];
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+            for (int b = 0; b < 2; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+    double *dst[4][2][2];
+    double cur[4][2][2];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int gi = ra + wr + a * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
+                dst[a][b][e] = (gi < N && gj <= gi) ? front_elem(A, s, nc, nr, N, gi, gj) : nullptr;
+                cur[a][b][e] = dst[a][b][e] ? *dst[a][b][e] : 0.0;
+            }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                if (dst[a][b][e]) *dst[a][b][e] = cur[a][b][e] - acc[a][b][e];
+}
+
 // ------------------------------------------------------------------------------- triangular solves
 struct SArgs {
     const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
     const int64_t *sn_rowptr, *Lp;
-    const double *Lx;
+    const double *Lx, *Xout;   // fronts of order N > bigN read their panel from Xout
+    int bigN;
     double *xs, *uv;
 };
 // forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t (unit lower); z_s = D^{-1} y_s is stored;
@@ -346,7 +477,7 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
     __shared__ double D[NB][NB + 1];
     const int s = list[blockIdx.x];
     const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
-    const double *L = A.Lx + A.Lp[s];
+    const double *L = (N > A.bigN ? A.Xout : A.Lx) + A.Lp[s];
     const int tid = threadIdx.x, lane = tid & 31;
     double *yb = vec + N;
     for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : 0.0;
@@ -404,7 +535,7 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
     __shared__ double D[NB][NB + 1];
     const int s = list[blockIdx.x];
     const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
-    const double *L = A.Lx + A.Lp[s];
+    const double *L = (N > A.bigN ? A.Xout : A.Lx) + A.Lp[s];
     const int *rows = A.rows + A.sn_rowptr[s];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NW = NT / 32;
     for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : A.xs[rows[i - nc]];
@@ -462,7 +593,7 @@ static FArgs fargs(qpdo_dev *d)
     Factor &F = d->F;
     FArgs A;
     A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
-    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Up = F.Up; A.Lx = F.Lx; A.Ux = F.Ux; A.sc = d->sc;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Up = F.Up; A.Lx = F.Lx; A.Ux = F.Ux; A.Xout = F.Xout; A.sc = d->sc;
     return A;
 }
 static SArgs sargs(qpdo_dev *d)
@@ -470,7 +601,7 @@ static SArgs sargs(qpdo_dev *d)
     Factor &F = d->F;
     SArgs A;
     A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
-    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.xs = F.xs; A.uv = F.uv;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.Xout = F.Xout; A.bigN = BUCKET_N[3]; A.xs = F.xs; A.uv = F.uv;
     return A;
 }
 
@@ -584,7 +715,7 @@ static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
         f_upload(d, &F.Kq, (const int *)S->Kq, S->nnzK) || f_upload(d, &F.Kdst, (const int64_t *)S->Kdst, S->nnzK) ||
         f_upload(d, &F.Ktp, (const int64_t *)S->Ktp, S->nnzK + 1) || f_upload(d, &F.Kt_row, (const int *)S->Kt_row, S->ntriple) ||
         f_upload(d, &F.Kt_a1, (const int *)S->Kt_a1, S->ntriple) || f_upload(d, &F.Kt_a2, (const int *)S->Kt_a2, S->ntriple) ||
-        f_alloc(d, &F.Kt_val, S->ntriple) || f_alloc(d, &F.Lx, S->lnz_stored) || f_alloc(d, &F.Ux, S->usize) ||
+        f_alloc(d, &F.Kt_val, S->ntriple) || f_alloc(d, &F.Lx, S->lnz_stored) || f_alloc(d, &F.Xout, S->max_front > BUCKET_N[3] ? S->lnz_stored : 1) || f_alloc(d, &F.Ux, S->usize) ||
         f_alloc(d, &F.uv, nrows))
         return -1;
     // launch plan: per level, fronts are sorted by decreasing order N
@@ -657,14 +788,8 @@ static long issue_factor(qpdo_dev *d)
             if (L.kind == 2) {
                 k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, d->st>>>(A, list); launches++;
                 for (int kb = 0; kb < L.maxnc; kb += NB) {
-                    k_big_potrf<<<L.count, 32, 0, d->st>>>(A, list, kb); launches++;
-                    int R = L.maxN - kb - 1;
-                    if (R > 0) {
-                        k_big_trsm<<<dim3(L.count, cdiv(R, 128)), 128, 0, d->st>>>(A, list, kb);
-                        int nt = cdiv(R, TS);
-                        k_big_syrk<<<dim3(L.count, nt * (nt + 1) / 2), 256, 0, d->st>>>(A, list, kb);
-                        launches += 2;
-                    }
+                    const int R = L.maxN - kb - 1, nt = R > 0 ? cdiv(R, TS) : 0;
+                    k_big_panel<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, d->st>>>(A, list, kb); launches++;
                 }
             } else {
                 size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 8 * (size_t)L.maxN);
