@@ -243,3 +243,20 @@ def test_full_size_lasso_path_against_reference_golden():
         if j == last:
             assert rel_err(g["pathlast_x"], x[::stride]) <= TOL and rel_err(g["pathlast_y"], y[::stride]) <= TOL
     s.delete()
+
+
+def test_edge_cases_no_constraints_and_scalar_problem(oracle_mod):
+    """m = 0 (the Newton matrix is Q + sigma I only, newton.c:21,31-33) and n = m = 1, against the restatement
+    (which the live reference agrees with: ref m=0 -> 6 loop passes / 2 outer, n=1 -> 10 / 4)"""
+    cases = [dict(Q=sp.csc_matrix(np.array([[2.0, 0.5], [0.5, 1.0]])), q=np.array([1.0, -1.0]), A=sp.csc_matrix((0, 2)),
+                  l=np.zeros(0), u=np.zeros(0)),
+             dict(Q=sp.csc_matrix(np.array([[1.0]])), q=np.array([-3.0]), A=sp.csc_matrix(np.array([[1.0]])),
+                  l=np.array([-1.0]), u=np.array([1.0]))]
+    expect = [(1, 6, 2), (1, 10, 4)]
+    for p, e in zip(cases, expect):
+        o = oracle_mod.solve(p)
+        r = gpu_solve(p)
+        assert (o.status_val, o.iterations, o.oterations) == e
+        assert (r.status_val, r.iterations, r.oterations) == e
+        assert rel_err(o.x, r.x) <= TOL and (o.y.size == 0 or rel_err(o.y, r.y) <= TOL)
+        assert abs(r.objective - o.objective) <= TOL * max(1.0, abs(o.objective))
