@@ -845,7 +845,7 @@ struct qpdo_batch {
     BatchPlan P;
     size_t smem = 0;
     int ctas = 0;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st2 = nullptr;     // st2: second lane of the chunked host-buffer pipeline
     std::vector<void *> allocs;
     // staging for the host-buffer entry point
     double *dQx = nullptr, *dAx = nullptr, *dq = nullptr, *dl = nullptr, *du = nullptr, *dc = nullptr, *dx0 = nullptr, *dy0 = nullptr;
@@ -880,10 +880,12 @@ extern "C" void qpdo_batch_destroy(qpdo_batch *b)
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->st) cudaStreamSynchronize(b->st);
+    if (b->st2) cudaStreamSynchronize(b->st2);
     for (void *p : b->allocs) cudaFree(p);
     if (b->e0) cudaEventDestroy(b->e0);
     if (b->e1) cudaEventDestroy(b->e1);
     if (b->st) cudaStreamDestroy(b->st);
+    if (b->st2) cudaStreamDestroy(b->st2);
     delete b;
 }
 
@@ -1070,19 +1072,36 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_solve, BNT, b->smem);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         b->ctas = std::max(1, per_sm) * std::max(1, sms);
-        if (cudaStreamCreateWithFlags(&b->st, cudaStreamNonBlocking) != cudaSuccess) { qpdo_set_error("cudaStreamCreate failed"); break; }
+        if (cudaStreamCreateWithFlags(&b->st, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&b->st2, cudaStreamNonBlocking) != cudaSuccess) { qpdo_set_error("cudaStreamCreate failed"); break; }
         cudaEventCreate(&b->e0); cudaEventCreate(&b->e1);
         const size_t cap = (size_t)capacity;
         if (b_alloc(b, &b->dQx, cap * nnzQ) || b_alloc(b, &b->dAx, cap * nnzA) || b_alloc(b, &b->dq, cap * n) || b_alloc(b, &b->dl, cap * m) ||
             b_alloc(b, &b->du, cap * m) || b_alloc(b, &b->dc, cap) || b_alloc(b, &b->dx0, cap * n) || b_alloc(b, &b->dy0, cap * m) ||
             b_alloc(b, &b->dx, cap * n) || b_alloc(b, &b->dy, cap * m) || b_alloc(b, &b->dsum, cap) || b_alloc(b, &b->dact, cap * m) ||
-            b_alloc(b, &b->next, 1))
+            b_alloc(b, &b->next, 2))
             break;
         rc = 0;
     } while (0);
     qpdo_symbolic_free(S);
     if (rc) { qpdo_batch_destroy(b); return rc; }
     *out = b;
+    return 0;
+}
+
+static int batch_launch(qpdo_batch *b, cudaStream_t st, int *next, int first, int count, const double *dQx, const double *dAx,
+                        const double *dq, const double *dl, const double *du, const double *dc, const double *dx0, const double *dy0,
+                        double *dx, double *dy, qpdo_batch_summary *dsummary, unsigned char *dactive)
+{   // instances first .. first + count - 1 of the given (instance-major) device arrays
+    const size_t o = (size_t)first, n = b->n, m = b->m;
+    BatchIO io;
+    io.Qx = dQx + o * b->nnzQ; io.Ax = dAx + o * b->nnzA; io.q = dq + o * n; io.l = dl + o * m; io.u = du + o * m;
+    io.c = dc ? dc + o : nullptr; io.x0 = dx0 ? dx0 + o * n : nullptr; io.y0 = dy0 ? dy0 + o * m : nullptr;
+    io.x = dx ? dx + o * n : nullptr; io.y = dy ? dy + o * m : nullptr; io.summary = dsummary ? dsummary + o : nullptr;
+    io.active = dactive ? dactive + o * m : nullptr; io.count = count; io.next = next;
+    io.timing = b->timing ? b->timing + o * 8 : nullptr;
+    CUDA_OK(cudaMemsetAsync(next, 0, sizeof(int), st));
+    k_batch_solve<<<std::min(count, b->ctas), BNT, b->smem, st>>>(b->P, io);
+    CUDA_OK(cudaGetLastError());
     return 0;
 }
 
@@ -1094,14 +1113,8 @@ extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *d
     if (!b || count < 0 || !dQx || !dAx || !dq || !dl || !du) { qpdo_set_error("qpdo_batch_solve_device: bad arguments"); return -3; }
     if (count == 0) return 0;
     CUDA_OK(cudaSetDevice(b->device));
-    BatchIO io;
-    io.Qx = dQx; io.Ax = dAx; io.q = dq; io.l = dl; io.u = du; io.c = dc; io.x0 = dx0; io.y0 = dy0;
-    io.x = dx; io.y = dy; io.summary = dsummary; io.active = dactive; io.count = count; io.next = b->next; io.timing = b->timing;
-    CUDA_OK(cudaMemsetAsync(b->next, 0, sizeof(int), b->st));
     if (kernel_ms) CUDA_OK(cudaEventRecord(b->e0, b->st));
-    const int grid = std::min(count, b->ctas);
-    k_batch_solve<<<grid, BNT, b->smem, b->st>>>(b->P, io);
-    CUDA_OK(cudaGetLastError());
+    if (batch_launch(b, b->st, b->next, 0, count, dQx, dAx, dq, dl, du, dc, dx0, dy0, dx, dy, dsummary, dactive)) return -1;
     if (kernel_ms) CUDA_OK(cudaEventRecord(b->e1, b->st));
     if (sync || kernel_ms) {
         CUDA_OK(cudaStreamSynchronize(b->st));
@@ -1117,23 +1130,33 @@ extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, cons
     if (!b || count < 0 || count > b->capacity || !Qx || !Ax || !q || !l || !u) { qpdo_set_error("qpdo_batch_solve: bad arguments (count > capacity?)"); return -3; }
     if (count == 0) return 0;
     CUDA_OK(cudaSetDevice(b->device));
-    const size_t cn = (size_t)count, n = b->n, m = b->m, D = sizeof(double);
-    CUDA_OK(cudaMemcpyAsync(b->dQx, Qx, D * cn * b->nnzQ, cudaMemcpyHostToDevice, b->st));
-    CUDA_OK(cudaMemcpyAsync(b->dAx, Ax, D * cn * b->nnzA, cudaMemcpyHostToDevice, b->st));
-    CUDA_OK(cudaMemcpyAsync(b->dq, q, D * cn * n, cudaMemcpyHostToDevice, b->st));
-    if (m) CUDA_OK(cudaMemcpyAsync(b->dl, l, D * cn * m, cudaMemcpyHostToDevice, b->st));
-    if (m) CUDA_OK(cudaMemcpyAsync(b->du, u, D * cn * m, cudaMemcpyHostToDevice, b->st));
-    if (c) CUDA_OK(cudaMemcpyAsync(b->dc, c, D * cn, cudaMemcpyHostToDevice, b->st));
-    if (x0) CUDA_OK(cudaMemcpyAsync(b->dx0, x0, D * cn * n, cudaMemcpyHostToDevice, b->st));
-    if (y0 && m) CUDA_OK(cudaMemcpyAsync(b->dy0, y0, D * cn * m, cudaMemcpyHostToDevice, b->st));
-    if (qpdo_batch_solve_device(b, count, b->dQx, b->dAx, b->dq, b->dl, b->du, c ? b->dc : nullptr, x0 ? b->dx0 : nullptr,
-                                (y0 && m) ? b->dy0 : nullptr, b->dx, b->dy, b->dsum, b->dact, 0, nullptr))
-        return -1;
-    if (x) CUDA_OK(cudaMemcpyAsync(x, b->dx, D * cn * n, cudaMemcpyDeviceToHost, b->st));
-    if (y && m) CUDA_OK(cudaMemcpyAsync(y, b->dy, D * cn * m, cudaMemcpyDeviceToHost, b->st));
-    if (summary) CUDA_OK(cudaMemcpyAsync(summary, b->dsum, sizeof(qpdo_batch_summary) * cn, cudaMemcpyDeviceToHost, b->st));
-    if (active_set && m) CUDA_OK(cudaMemcpyAsync(active_set, b->dact, cn * m, cudaMemcpyDeviceToHost, b->st));
+    const size_t n = b->n, m = b->m, D = sizeof(double);
+    // chunks alternate between two streams: the host->device copy of chunk k+1 and the device->host copy of
+    // chunk k-1 overlap the kernel of chunk k (with pinned host buffers; pageable ones just serialise)
+    const int nchunk = count >= 8 * b->ctas ? 8 : 1;
+    for (int k = 0; k < nchunk; k++) {
+        const int lo = (int)((long)count * k / nchunk), hi = (int)((long)count * (k + 1) / nchunk), cn = hi - lo;
+        if (cn <= 0) continue;
+        cudaStream_t st = (k & 1) ? b->st2 : b->st;
+        const size_t o = (size_t)lo;
+        CUDA_OK(cudaMemcpyAsync(b->dQx + o * b->nnzQ, Qx + o * b->nnzQ, D * cn * b->nnzQ, cudaMemcpyHostToDevice, st));
+        CUDA_OK(cudaMemcpyAsync(b->dAx + o * b->nnzA, Ax + o * b->nnzA, D * cn * b->nnzA, cudaMemcpyHostToDevice, st));
+        CUDA_OK(cudaMemcpyAsync(b->dq + o * n, q + o * n, D * cn * n, cudaMemcpyHostToDevice, st));
+        if (m) CUDA_OK(cudaMemcpyAsync(b->dl + o * m, l + o * m, D * cn * m, cudaMemcpyHostToDevice, st));
+        if (m) CUDA_OK(cudaMemcpyAsync(b->du + o * m, u + o * m, D * cn * m, cudaMemcpyHostToDevice, st));
+        if (c) CUDA_OK(cudaMemcpyAsync(b->dc + o, c + o, D * cn, cudaMemcpyHostToDevice, st));
+        if (x0) CUDA_OK(cudaMemcpyAsync(b->dx0 + o * n, x0 + o * n, D * cn * n, cudaMemcpyHostToDevice, st));
+        if (y0 && m) CUDA_OK(cudaMemcpyAsync(b->dy0 + o * m, y0 + o * m, D * cn * m, cudaMemcpyHostToDevice, st));
+        if (batch_launch(b, st, b->next + (k & 1), lo, cn, b->dQx, b->dAx, b->dq, b->dl, b->du, c ? b->dc : nullptr, x0 ? b->dx0 : nullptr,
+                         (y0 && m) ? b->dy0 : nullptr, b->dx, b->dy, b->dsum, b->dact))
+            return -1;
+        if (x) CUDA_OK(cudaMemcpyAsync(x + o * n, b->dx + o * n, D * cn * n, cudaMemcpyDeviceToHost, st));
+        if (y && m) CUDA_OK(cudaMemcpyAsync(y + o * m, b->dy + o * m, D * cn * m, cudaMemcpyDeviceToHost, st));
+        if (summary) CUDA_OK(cudaMemcpyAsync(summary + o, b->dsum + o, sizeof(qpdo_batch_summary) * cn, cudaMemcpyDeviceToHost, st));
+        if (active_set && m) CUDA_OK(cudaMemcpyAsync(active_set + o * m, b->dact + o * m, (size_t)cn * m, cudaMemcpyDeviceToHost, st));
+    }
     cudaError_t e = cudaStreamSynchronize(b->st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(b->st2);
     if (e != cudaSuccess) { qpdo_set_error("batch kernel failed: %s", cudaGetErrorString(e)); return -1; }
     return 0;
 }
