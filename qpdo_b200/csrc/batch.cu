@@ -50,7 +50,8 @@ struct BatchPlan {
     const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
     const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
     int max_front, ucolw;
-    const int *Eptr, *Emap;                  // owned-entry enumeration of each front: i | j << 8, column major, j >= 1, i = j..N
+    const int2 *Emap2;                       // owned entries of each front: {i | j << 8, position in L or ~index into xs}, column major, j >= 1, i = j..N
+    const int4 *sn_desc;                     // per supernode {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
     // settings (reference include/types.h:96-116)
     int max_iter, inner_max_iter, proximal, scaling, reset_newton_iter;
     double eps_abs, eps_abs_in, eps_prim_inf, eps_dual_inf, rho, theta, delta, mu_min, sigma_init, sigma_upd, sigma_min;
@@ -239,13 +240,17 @@ __device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, 
 #define SN_NMAX 31              // b_backward_sn: front order limit (one lane per front row)
 __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + jj * N - ((jj * (jj - 1)) >> 1) - jj; }   // + front row i
 #define SN_EPT 8
+#define SN_DESC_MAX 64          // supernode descriptors cached in shared memory (else read from global)
+__shared__ int4 s_desc[2 * SN_DESC_MAX];   // {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
+__device__ __forceinline__ int4 sn_desc(const BatchPlan &P, int s, int which) { return P.nsuper <= SN_DESC_MAX ? s_desc[2 * s + which] : P.sn_desc[2 * s + which]; }
 __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
     const int tid = threadIdx.x;
     for (int s = 0; s < P.nsuper; s++) {
-        const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
-        const int *rows = P.Srow + P.Sptr[s], *up = P.Upos + P.Uptr[s], *emap = P.Emap + P.Eptr[s];
-        const int ne = P.Eptr[s + 1] - P.Eptr[s], ept = (ne + BNT - 1) / BNT;
+        const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
+        const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
+        const int2 *emap = P.Emap2 + d1.y;
+        const int ne = d1.z, ept = (ne + BNT - 1) / BNT;
         double *lcol = ucol + N + 1;
         int eij[SN_EPT];            // i | j << 8;  j == 0 never updates
         double *ea[SN_EPT];
@@ -254,11 +259,9 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
             eij[e] = 0; ea[e] = L;
             const int idx = tid + e * BNT;
             if (e < ept && idx < ne) {
-                const int code = emap[idx], i = code & 255, j = code >> 8;
-                eij[e] = code;
-                if (i == N) ea[e] = xs + (j < nc ? f + j : rows[j - nc]);
-                else if (j < nc) ea[e] = L + sn_col(base, j, N) + i;
-                else ea[e] = L + up[(j - nc) * nr + (i - nc)];
+                const int2 em = emap[idx];                    // i | j << 8, position in L (>= 0) or ~index into xs
+                eij[e] = em.x;
+                ea[e] = em.y >= 0 ? L + em.y : xs + ~em.y;
             }
         }
         for (int k = 0; k < nc; k++) {
@@ -298,8 +301,9 @@ __device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, 
 {
     const int lane = threadIdx.x & 31;
     for (int s = P.nsuper - 1; s >= 0; s--) {
-        const int f = P.sn_f[s], nc = P.sn_nc[s], nr = P.sn_nr[s], N = nc + nr, base = P.sn_base[s];
-        const int *rows = P.Srow + P.Sptr[s];
+        const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
+        const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
+        const int *rows = P.Srow + d1.x;
         const int mycol = sn_col(base, lane, N);
         double col[SN_NMAX];
 #pragma unroll
@@ -829,6 +833,7 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const BatchPlan 
     V.red = p; p += BNW * 8;
     V.ucol = p; p += 2 * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
+    if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) s_b = atomicAdd(io.next, 1);
@@ -978,12 +983,6 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             }
             return sn_base[sn] + jj * N - jj * (jj - 1) / 2 - jj + fr;
         };
-        std::vector<int> Eptr(S->nsuper + 1, 0), Emap;
-        for (int sn = 0; sn < S->nsuper; sn++) {
-            const int N = sn_nc[sn] + sn_nr[sn];
-            for (int j = 1; j < N; j++) for (int i = j; i <= N; i++) Emap.push_back(i | (j << 8));
-            Eptr[sn + 1] = (int)Emap.size();
-        }
         bool pattern_ok = true;
         for (int sn = 0; sn < S->nsuper; sn++) {
             const int nr = sn_nr[sn];
@@ -996,6 +995,25 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             Uptr[sn + 1] = (int)Upos.size();
         }
         if (!pattern_ok) mode = 0;
+        // owned entries of every front with their final shared-memory positions, supernode descriptors
+        std::vector<int2> Emap2;
+        std::vector<int4> sn_desc(2 * (size_t)S->nsuper);
+        for (int sn = 0; sn < S->nsuper; sn++) {
+            const int nc = sn_nc[sn], nr = sn_nr[sn], N = nc + nr, f = sn_f[sn];
+            const int *rows = Srow.data() + Sptr[sn];
+            const int e0 = (int)Emap2.size();
+            for (int j = 1; j < N; j++) for (int i = j; i <= N; i++) {
+                int2 em; em.x = i | (j << 8);
+                if (i == N) em.y = ~(j < nc ? f + j : rows[j - nc]);
+                else if (j < nc) em.y = sn_base[sn] + j * N - j * (j - 1) / 2 - j + i;
+                else em.y = Upos[Uptr[sn] + (j - nc) * nr + (i - nc)];
+                Emap2.push_back(em);
+            }
+            int4 d0, d1;
+            d0.x = f; d0.y = nc; d0.z = nr; d0.w = sn_base[sn];
+            d1.x = Sptr[sn]; d1.y = e0; d1.z = (int)Emap2.size() - e0; d1.w = 0;
+            sn_desc[2 * sn] = d0; sn_desc[2 * sn + 1] = d1;
+        }
         // K entries -> packed positions
         const int nnzK = (int)S->nnzK;
         int P_nKround = 0;
@@ -1054,7 +1072,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kround, Kround) || b_upload(b, &P.Kmeta, Kmeta) || b_upload(b, &P.Ktr, Ktr) ||
             b_upload(b, &P.sn_f, sn_f) || b_upload(b, &P.sn_nc, sn_nc) || b_upload(b, &P.sn_nr, sn_nr) || b_upload(b, &P.sn_base, sn_base) ||
             b_upload(b, &P.Sptr, Sptr) || b_upload(b, &P.Srow, Srow) || b_upload(b, &P.Uptr, Uptr) || b_upload(b, &P.Upos, Upos) ||
-            b_upload(b, &P.Eptr, Eptr) || b_upload(b, &P.Emap, Emap) ||
+            b_upload(b, &P.Emap2, Emap2) || b_upload(b, &P.sn_desc, sn_desc) ||
             b_upload(b, &P.Lcp, Lcp) || b_upload(b, &P.Lri, Lri) || b_upload(b, &P.Lrp, Lrp) || b_upload(b, &P.Lci, Lci))
             break;
         P.max_iter = (int)s->max_iter; P.inner_max_iter = (int)s->inner_max_iter; P.proximal = (int)s->proximal; P.scaling = (int)s->scaling;
