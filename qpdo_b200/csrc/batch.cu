@@ -392,8 +392,43 @@ __device__ double b_linesearch(const BatchPlan &P, const BVec &V)
     double eta = s[0]; eta += s[1]; eta *= 0.5;
     double beta = s[2]; beta += s[3]; beta *= 0.5;
     double r3[3] = {0, 0, 0};                  // aJ, bJ, nL
-    for (int k = tid; k < P2; k += BNT) {
-        if (k < M2) {                          // linesearch.c:28-39,82-114
+    // the breakpoints with t > 0 are compacted to the front of key / idx (ballot prefix sums), so that the
+    // bitonic network only spans next_pow2(nL) slots instead of next_pow2(2m); (key, idx) is a total order,
+    // the sorted prefix does not depend on where the pairs started
+    constexpr int RLMAX = 8;
+    const bool compact = P2 <= RLMAX * BNT;
+    __shared__ int cw[RLMAX * BNW];
+    unsigned long long kreg[RLMAX];
+    int lpre[RLMAX];
+#pragma unroll
+    for (int r = 0; r < RLMAX; r++) {
+        const int k = tid + r * BNT;
+        kreg[r] = ~0ull; lpre[r] = 0;
+        if (k < P2) {
+            unsigned long long kk = ~0ull;
+            if (k < M2) {                          // linesearch.c:28-39,82-114
+                const int i = k < m ? k : k - m;
+                double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
+                double c0 = V.Adx[i] + (-1.0) * tm;
+                double dl = c0 * V.smu[i], al;
+                if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
+                else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
+                delta[k] = dl; alpha[k] = al;
+                const double t = al / dl;
+                const bool L = t > 0.0, Pp = dl > 0.0;
+                if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
+                if (L) { r3[2] += 1.0; kk = (unsigned long long)__double_as_longlong(t); }
+            }
+            if (compact) {
+                const unsigned bal = __ballot_sync(0xffffffffu, kk != ~0ull);
+                kreg[r] = kk; lpre[r] = __popc(bal & ((1u << lane) - 1u));
+                if (lane == 0) cw[r * BNW + wid] = __popc(bal);
+            } else { key[k] = kk; idx[k] = k < M2 ? k : 0; }
+        } else if (compact && lane == 0) cw[r * BNW + wid] = 0;
+    }
+    for (int k = tid + RLMAX * BNT; k < P2; k += BNT) {    // only when !compact (2m > RLMAX * BNT / 2 ... large m)
+        unsigned long long kk = ~0ull;
+        if (k < M2) {
             const int i = k < m ? k : k - m;
             double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
             double c0 = V.Adx[i] + (-1.0) * tm;
@@ -404,10 +439,9 @@ __device__ double b_linesearch(const BatchPlan &P, const BVec &V)
             const double t = al / dl;
             const bool L = t > 0.0, Pp = dl > 0.0;
             if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
-            if (L) { r3[2] += 1.0; key[k] = (unsigned long long)__double_as_longlong(t); }
-            else key[k] = ~0ull;
-            idx[k] = k;
-        } else { key[k] = ~0ull; idx[k] = 0; }
+            if (L) { r3[2] += 1.0; kk = (unsigned long long)__double_as_longlong(t); }
+        }
+        key[k] = kk; idx[k] = k < M2 ? k : 0;
     }
     block_sum<3>(r3, red);
     const int nLt = (int)(r3[2] + 0.5);
@@ -428,10 +462,25 @@ __device__ double b_linesearch(const BatchPlan &P, const BVec &V)
     }
     const double a0 = eta + aJ, b0 = beta - bJ;
     if (tid == 0) kmin = nLt;
+    int P2e = P2;
+    if (compact) {
+        P2e = 2;
+        while (P2e < nLt) P2e <<= 1;
+        int base = 0;
+#pragma unroll
+        for (int r = 0; r < RLMAX; r++) {
+            if (r * BNT < P2) {
+                int mine = base;
+                for (int w = 0; w < BNW; w++) { const int c = cw[r * BNW + w]; if (w < wid) mine += c; base += c; }
+                if (kreg[r] != ~0ull) { key[mine + lpre[r]] = kreg[r]; idx[mine + lpre[r]] = tid + r * BNT; }
+            }
+        }
+        for (int k = nLt + tid; k < P2e; k += BNT) { key[k] = ~0ull; idx[k] = 0; }
+    }
     __syncthreads();
-    for (int size = 2; size <= P2; size <<= 1)
+    for (int size = 2; size <= P2e; size <<= 1)
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int t = tid; t < (P2 >> 1); t += BNT) {
+            for (int t = tid; t < (P2e >> 1); t += BNT) {
                 const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
                 const bool up = ((lo & size) == 0);
                 const unsigned long long ka = key[lo], kb = key[hi];
