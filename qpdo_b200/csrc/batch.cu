@@ -30,8 +30,14 @@
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
 
+// gather SpMV program: rows dealt to the threads in rounds of BNT (row = round * BNT + thread), the terms of a
+// round slot-major (a warp reads 32 consecutive 4-byte records per slot; uniform trip count, several loads in
+// flight); record = value index | column << 16 | second-half flag << 31, 0xffffffff = padding
+struct BatchEll { int nround; const int2 *round; const unsigned *rec; };
+
 struct BatchPlan {
     int n, m, nnzA, nnzQ, nnzK, nKpack, karea, P2;
+    BatchEll ellA, ellAt, ellQ;              // y = A x (rows of A), y = A' x (columns of A), y = Q x (full symmetric rows)
     // shared structure (device pointers)
     const int *Ap, *Ai;                      // CSC of A
     const int *Rp, *Rj, *Rsrc;               // CSR of A (Rsrc: index into the CSC values)
@@ -126,32 +132,56 @@ __device__ __forceinline__ double bclamp(double a, double lo, double hi)
 // ------------------------------------------------------------------------------- SpMV (cholmod_sdmult order)
 __device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, const double *x, double *y)
 {   // CSR gather in ascending column order == CSC scatter order (t_cholmod_sdmult.c:297-320)
-    for (int i = threadIdx.x; i < P.m; i += BNT) {
+    for (int r = 0; r < P.ellA.nround; r++) {
+        const int2 rk = P.ellA.round[r];
+        const unsigned *T = P.ellA.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
-        for (int k = P.Rp[i]; k < P.Rp[i + 1]; k++) s += Av[P.Rsrc[k]] * x[P.Rj[k]];
-        y[i] = s;
+#pragma unroll 4
+        for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += Av[w & 0xffffu] * x[w >> 16]; }
+        const int i = r * BNT + threadIdx.x;
+        if (i < P.m) y[i] = s;
     }
 }
 __device__ __forceinline__ void b_spmv_At(const BatchPlan &P, const double *Av, const double *x, double *y)
 {   // t_cholmod_sdmult.c:141-165
-    for (int j = threadIdx.x; j < P.n; j += BNT) {
+    for (int r = 0; r < P.ellAt.nround; r++) {
+        const int2 rk = P.ellAt.round[r];
+        const unsigned *T = P.ellAt.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
-        for (int k = P.Ap[j]; k < P.Ap[j + 1]; k++) s += Av[k] * x[P.Ai[k]];
-        y[j] = s;
+#pragma unroll 4
+        for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += Av[w & 0xffffu] * x[w >> 16]; }
+        const int j = r * BNT + threadIdx.x;
+        if (j < P.n) y[j] = s;
     }
 }
 __device__ __forceinline__ void b_spmv_Q(const BatchPlan &P, const double *Qv, const double *x, double *y)
-{   // t_cholmod_sdmult.c:440-484 (split sum)
-    for (int i = threadIdx.x; i < P.n; i += BNT) {
-        const int b = P.Fp[i], mid = b + P.Fdiag[i], e = P.Fp[i + 1];
+{   // t_cholmod_sdmult.c:440-484 (split sum: the terms of the lower-triangular columns, then the mirrored ones)
+    for (int r = 0; r < P.ellQ.nround; r++) {
+        const int2 rk = P.ellQ.round[r];
+        const unsigned *T = P.ellQ.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s1 = 0.0, s2 = 0.0;
-        for (int k = b; k < mid; k++) s1 += Qv[P.Fsrc[k]] * x[P.Fj[k]];
-        for (int k = mid; k < e; k++) s2 += Qv[P.Fsrc[k]] * x[P.Fj[k]];
-        y[i] = s1 + s2;
+#pragma unroll 4
+        for (int k = 0; k < rk.y; k++) {
+            const unsigned w = T[(size_t)k * BNT];
+            if (w != 0xffffffffu) {
+                const double t = Qv[w & 0xffffu], v = x[(w >> 16) & 0x7fffu];
+                if ((int)w >= 0) s1 += t * v; else s2 += t * v;
+            }
+        }
+        const int i = r * BNT + threadIdx.x;
+        if (i < P.n) y[i] = s1 + s2;
     }
 }
 
 // ------------------------------------------------------------------------------- KKT matrix, LDL', solves
+// u / d with r = RN(1/d): one Newton correction of RN(u r) gives the correctly rounded quotient (same bits
+// as the division operator) without DDIV's slow path for zero or tiny numerators
+__device__ __forceinline__ double b_div(double u, double d, double r)
+{
+    const double q0 = __dmul_rn(u, r);
+    return fma(fma(-q0, d, u), r, q0);
+}
+
 __device__ __forceinline__ int koff(int j, int n) { return j * n - ((j * (j - 1)) >> 1) - j; }   // (i, j), i >= j, at koff(j) + i
 
 // K = Q + sigma I + A' diag(omega) A in the permuted packed lower triangle: the fused replacement
@@ -645,7 +675,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
                 const double z = bclamp(w, l, u);
                 const double rpi = Ax + mu * (yb - y) - z;
                 V.rpi[i] = rpi;
-                const double Einv = scaled ? 1.0 / V.E[i] : 1.0;
+                const double Einv = scaled ? __drcp_rn(V.E[i]) : 1.0;
                 double a = fabs(scaled ? Einv * rp : rp), bb = fabs(scaled ? Einv * rpi : rpi);
                 nr[0] = a > nr[0] ? a : nr[0]; nr[1] = bb > nr[1] ? bb : nr[1];
             }
@@ -656,7 +686,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
                 V.df[i] = df;
                 const double rdi = df + V.Aty[i];
                 V.rdi[i] = rdi;
-                const double Dinv = scaled ? 1.0 / V.D[i] : 1.0;
+                const double Dinv = scaled ? __drcp_rn(V.D[i]) : 1.0;
                 double a = fabs(scaled ? Dinv * rd : rd), bb = fabs(scaled ? Dinv * rdi : rdi);
                 nr[2] = a > nr[2] ? a : nr[2]; nr[3] = bb > nr[3] ? bb : nr[3];
             }
@@ -684,7 +714,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
                             s1[0] += (V.u[i] < lim) ? V.u[i] * dp : 0.0;
                             s1[0] += (V.l[i] > -lim) ? V.l[i] * dm : 0.0;
                         }
-                        FOR_N(i) { double v = V.Atdy[i]; if (scaled) { v = (1.0 / V.D[i]) * v; V.Atdy[i] = v; } v = fabs(v); mx[0] = v > mx[0] ? v : mx[0]; }
+                        FOR_N(i) { double v = V.Atdy[i]; if (scaled) { v = __drcp_rn(V.D[i]) * v; V.Atdy[i] = v; } v = fabs(v); mx[0] = v > mx[0] ? v : mx[0]; }
                         block_sum<1>(s1, red);
                         block_max<1>(mx, red);
                         if (mx[0] <= en && s1[0] <= -en) {
@@ -706,7 +736,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
                         int viol = 0, d1, d2;
                         FOR_M(k) {
                             double a = V.Adx[k];
-                            if (scaled) { a = (1.0 / V.E[k]) * a; V.Adx[k] = a; }
+                            if (scaled) { a = __drcp_rn(V.E[k]) * a; V.Adx[k] = a; }
                             const double lim = scaled ? V.E[k] * 1e20 : 1e20;
                             if ((V.u[k] < lim && a >= en) || (V.l[k] > -lim && a <= -en)) viol = 1;
                         }
@@ -796,14 +826,14 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             else mode = 2;
             FOR_M(i) {      // row weights embodied in the factor + "dy" = (I+P) res_prim_in ./ mu (newton.c:37-40)
                 const int a = V.act[i], o = V.acto[i];
-                const double inv = 1.0 / V.mu[i];
+                const double mui = V.mu[i], inv = __drcp_rn(mui);
                 double om;
                 if (mode == 0) om = a ? inv : 0.0;
                 else if (mode == 1) { om = V.om[i]; if (a && !o) om = om + inv; if (!a && o) om = om - inv; }
                 else om = 0.0;
                 V.om[i] = om;
                 V.acto[i] = (unsigned char)a;
-                double v = V.rpi[i] / V.mu[i];
+                double v = b_div(V.rpi[i], mui, inv);
                 if (!a) v = v * 2.0;
                 V.dy[i] = v;
             }
@@ -830,7 +860,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
             b_spmv_A(P, V.Av, V.dx, V.Adx);
             __syncthreads();
             if (proximal) { FOR_N(i) V.Qdx[i] = V.Qdx[i] + sigma * V.dx[i]; }
-            FOR_M(i) { if (V.act[i]) V.dy[i] = V.dy[i] + V.Adx[i] / V.mu[i]; }
+            FOR_M(i) { if (V.act[i]) { const double mui = V.mu[i]; V.dy[i] = V.dy[i] + b_div(V.Adx[i], mui, __drcp_rn(mui)); } }
             __syncthreads();
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
             __syncthreads();
@@ -1105,6 +1135,35 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
             }
             P_nKround = nround;
         }
+        // gather programs of the three SpMVs (same term order per row as the CSR/CSC loops)
+        std::vector<int2> ellRound[3]; std::vector<unsigned> ellRec[3];
+        auto build_ell = [&](int which, int nrows, const std::vector<int> &ptr, const int *col, const int *src, const int *split) {
+            const int nround = (nrows + BNT - 1) / BNT;
+            for (int r = 0; r < nround; r++) {
+                int kmax = 0;
+                for (int t = 0; t < BNT && r * BNT + t < nrows; t++) kmax = std::max(kmax, ptr[r * BNT + t + 1] - ptr[r * BNT + t]);
+                int2 rk; rk.x = (int)(ellRec[which].size() / BNT); rk.y = kmax;
+                ellRound[which].push_back(rk);
+                const size_t base = ellRec[which].size();
+                ellRec[which].resize(base + (size_t)kmax * BNT, 0xffffffffu);
+                for (int t = 0; t < BNT && r * BNT + t < nrows; t++) {
+                    const int i = r * BNT + t;
+                    for (int k = ptr[i]; k < ptr[i + 1]; k++) {
+                        const unsigned sv = (unsigned)(src ? src[k] : k);
+                        unsigned w = sv | ((unsigned)col[k] << 16);
+                        if (split && k - ptr[i] >= split[i]) w |= 0x80000000u;
+                        ellRec[which][base + (size_t)(k - ptr[i]) * BNT + t] = w;
+                    }
+                }
+            }
+        };
+        if (nnzA >= 65536 || nnzQ >= 65536 || n >= 32768 || m >= 32768) { qpdo_set_error("qpdo_batch_create: problem does not fit the batch kernel's 16-bit index records"); break; }
+        {
+            std::vector<int> vAp0(Ap, Ap + n + 1);
+            build_ell(0, m, Rp, Rj.data(), Rsrc.data(), nullptr);
+            build_ell(1, n, vAp0, Ai, nullptr, nullptr);
+            build_ell(2, n, Fp, Fj.data(), Fsrc.data(), Fdiag.data());
+        }
         if (nnzA >= 65536) { qpdo_set_error("qpdo_batch_create: nnz(A) >= 65536 does not fit the batch kernel"); break; }
         std::vector<int> perm(S->perm, S->perm + n), vQp(Qp, Qp + n + 1), vQi(Qi, Qi + nnzQ), vAp(Ap, Ap + n + 1), vAi(Ai, Ai + nnzA);
         BatchPlan &P = b->P;
@@ -1116,6 +1175,9 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
+        P.ellA.nround = (int)ellRound[0].size(); P.ellAt.nround = (int)ellRound[1].size(); P.ellQ.nround = (int)ellRound[2].size();
+        if (b_upload(b, &P.ellA.round, ellRound[0]) || b_upload(b, &P.ellA.rec, ellRec[0]) || b_upload(b, &P.ellAt.round, ellRound[1]) ||
+            b_upload(b, &P.ellAt.rec, ellRec[1]) || b_upload(b, &P.ellQ.round, ellRound[2]) || b_upload(b, &P.ellQ.rec, ellRec[2])) break;
         if (b_upload(b, &P.Ap, vAp) || b_upload(b, &P.Ai, vAi) || b_upload(b, &P.Rp, Rp) || b_upload(b, &P.Rj, Rj) || b_upload(b, &P.Rsrc, Rsrc) ||
             b_upload(b, &P.Qp, vQp) || b_upload(b, &P.Qi, vQi) || b_upload(b, &P.Fp, Fp) || b_upload(b, &P.Fj, Fj) || b_upload(b, &P.Fsrc, Fsrc) ||
             b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kround, Kround) || b_upload(b, &P.Kmeta, Kmeta) || b_upload(b, &P.Ktr, Ktr) ||
