@@ -27,6 +27,10 @@
 #ifndef B_MINCTAS
 #define B_MINCTAS 4              // resident CTAs per SM the register budget is sized for
 #endif
+#ifndef B_KUNROLL
+#define B_KUNROLL 4            // K assembly: product records in flight per thread
+#endif
+constexpr int kKUnroll = B_KUNROLL;
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
 
@@ -199,7 +203,7 @@ __device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av,
         const int2 rk = P.Kround[r];                          // first slot, slots
         const uint2 *T = P.Ktr + (size_t)rk.x * BNT + threadIdx.x;
         double v = 0.0;
-#pragma unroll 4
+#pragma unroll (kKUnroll)
         for (int k = 0; k < rk.y; k++) {
             const uint2 w = T[(size_t)k * BNT];               // row (or -1: padding), a1 | a2 << 16
             if ((int)w.x >= 0) v = fma(om[w.x], Av[w.y & 0xffffu] * Av[w.y >> 16], v);
@@ -294,8 +298,60 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
                 ea[e] = em.y >= 0 ? L + em.y : xs + ~em.y;
             }
         }
-        for (int k = 0; k < nc; k++) {
+#ifdef B_NO_PAIRS
+        const bool pairs = false;
+#else
+        const bool pairs = N < 32;                              // rows k+1 .. N of a column pair sit in one warp
+#endif
+        double *u1c = ucol + 2 * (N + 1), *l1c = ucol + 3 * (N + 1);
+        int k = 0;
+        while (k < nc) {
             const int pc = sn_col(base, k, N);
+            if (pairs && k + 1 < nc) {
+                // two pivots per barrier pair: the lanes of warp 0 scale column k, apply its update to column k+1
+                // (and to the pivot d_{k+1}, redundantly in every lane) and scale column k+1 right away; the
+                // owners then apply both rank-1 updates.  Per entry the same fma's in the same order.
+                const int pc1 = sn_col(base, k + 1, N);
+                if (tid < N - k) {
+                    const unsigned mask = 0xffffffffu >> (32 - (N - k));
+                    const int i = k + 1 + tid;
+                    double *pa0 = (i < N) ? L + pc + i : xs + f + k;
+                    double *pa1 = (i < N) ? L + pc1 + i : xs + f + k + 1;          // lane 0: the pivot d_{k+1} itself
+                    const double u0 = *pa0, dk = L[pc + k], w = L[pc + k + 1], a1 = *pa1, d1raw = L[pc1 + k + 1];
+                    const double rk = __drcp_rn(dk);
+                    const double l0 = b_div(u0, dk, rk), lw = b_div(w, dk, rk);
+                    const double t1 = fma(-u0, lw, a1), d1 = fma(-w, lw, d1raw);
+                    const double r1 = __drcp_rn(d1);
+                    const double l1 = b_div(t1, d1, r1);
+                    __syncwarp(mask);                               // every lane has read w before lane 0 overwrites it
+                    ucol[i] = u0; lcol[i] = l0; *pa0 = l0;
+                    if (tid == 0) *pa1 = d1;
+                    else { u1c[i] = t1; l1c[i] = l1; *pa1 = l1; }
+                }
+                __syncthreads();
+#pragma unroll
+                for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
+                    double u0v[SN_EPT / 2], l0v[SN_EPT / 2], u1v[SN_EPT / 2], l1v[SN_EPT / 2], av[SN_EPT / 2];
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) {
+                        const int ij = eij[h + e];
+                        const bool on = h + e < ept && (ij >> 8) > k + 1;
+                        u0v[e] = on ? ucol[ij & 255] : 0.0; l0v[e] = on ? lcol[ij >> 8] : 0.0;
+                        u1v[e] = on ? u1c[ij & 255] : 0.0; l1v[e] = on ? l1c[ij >> 8] : 0.0;
+                        av[e] = on ? *ea[h + e] : 0.0;
+                    }
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++)
+                        if (h + e < ept && (eij[h + e] >> 8) > k + 1) *ea[h + e] = av[e];
+                }
+                __syncthreads();
+                k += 2;
+                continue;
+            }
             if (tid < N - k) {                                  // rows k+1 .. N (N = right-hand side)
                 const int i = k + 1 + tid;
                 double *pa = (i < N) ? L + pc + i : xs + f + k;
@@ -303,8 +359,8 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
                 // u / dk, correctly rounded (Markstein: reciprocal, product, one residual correction).  The plain
                 // quotient takes DDIV's ~60-instruction slow path whenever u == 0, which structural zeros of
                 // the front make the common case; this form never does and gives the same bits.
-                const double rk = __drcp_rn(dk), q0 = __dmul_rn(u, rk);
-                const double l = fma(fma(-q0, dk, u), rk, q0);
+                const double rk = __drcp_rn(dk);
+                const double l = b_div(u, dk, rk);
                 ucol[i] = u; lcol[i] = l; *pa = l;
             }
             __syncthreads();
@@ -322,6 +378,7 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
             for (int e = 0; e < SN_EPT; e++)
                 if (e < ept && (eij[e] >> 8) > k) *ea[e] = av[e];
             __syncthreads();
+            k++;
         }
     }
 }
@@ -910,7 +967,7 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const BatchPlan 
 #undef TAKE
     V.K = p; p += P.karea;
     V.red = p; p += BNW * 8;
-    V.ucol = p; p += 2 * P.ucolw;
+    V.ucol = p; p += 4 * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
     if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
     for (;;) {
@@ -1191,7 +1248,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.eps_abs = s->eps_abs; P.eps_abs_in = s->eps_abs_in; P.eps_prim_inf = s->eps_prim_inf; P.eps_dual_inf = s->eps_dual_inf;
         P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
         P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
-        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * (size_t)P.ucolw) + 2 * (size_t)m + 16;
+        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 4 * (size_t)P.ucolw) + 2 * (size_t)m + 16;
         if (b->smem > 227 * 1024) {
             qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
             break;

@@ -267,6 +267,32 @@ __global__ void __launch_bounds__(1024) k_sort_scan(unsigned *hist, int total)
     unsigned run = off + p - s;
     for (int i = b; i < e; i++) { unsigned v = hist[i]; hist[i] = run; run += v; }
 }
+// same scan with the table staged in shared memory (coalesced in, thread-sequential over an odd-stride chunk,
+// coalesced out): the global version is a chain of dependent L2 round trips, 40 us at 2m = 360,600
+#define SCAN_SMEM_MAX_PER 55     // 1024 chunks of at most this many entries fit 227 KB
+__global__ void __launch_bounds__(1024) k_sort_scan_smem(unsigned *hist, int total, int per)
+{
+    extern __shared__ unsigned sh[];
+    __shared__ unsigned ws[32];
+    const int tid = threadIdx.x, perp = per | 1;
+    for (int i = tid; i < total; i += 1024) sh[(i / per) * perp + (i % per)] = hist[i];
+    __syncthreads();
+    const int b = tid * per, cnt = max(0, min(total - b, per));
+    unsigned *mine = sh + tid * perp;
+    unsigned s = 0;
+    for (int j = 0; j < cnt; j++) s += mine[j];
+    unsigned p = s;
+    const int lane = tid & 31, wid = tid >> 5;
+    for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, p, o); if (lane >= o) p += t; }
+    if (lane == 31) ws[wid] = p;
+    __syncthreads();
+    unsigned off = 0;
+    for (int w = 0; w < wid; w++) off += ws[w];
+    unsigned run = off + p - s;
+    for (int j = 0; j < cnt; j++) { const unsigned v = mine[j]; mine[j] = run; run += v; }
+    __syncthreads();
+    for (int i = tid; i < total; i += 1024) hist[i] = sh[(i / per) * perp + (i % per)];
+}
 __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const unsigned long long *key, const int *idx, int N, int shift,
                                                               const unsigned *hist, int nblk, unsigned long long *okey, int *oidx)
 {
@@ -378,6 +404,11 @@ __global__ void k_sweep_final(const double *cand, int nblk, const double *bs, co
 // =============================================================================== host side
 int linesearch_setup(qpdo_dev *d)
 {
+    static bool attr_done = false;
+    if (!attr_done) {
+        CUDA_OK(cudaFuncSetAttribute(k_sort_scan_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(unsigned) * 1024 * (SCAN_SMEM_MAX_PER | 1))));
+        attr_done = true;
+    }
     const size_t M2 = 2 * (size_t)d->m;
     d->sort_blocks = std::max(1, cdiv((long)M2, SORT_TILE));
     d->ls_blocks = std::max(1, std::min(592, cdiv(std::max(d->n, 2 * d->m), 256)));
@@ -411,7 +442,9 @@ int linesearch_run(qpdo_dev *d)
     for (int pass = 0; pass < 8; pass++) {
         const int shift = 8 * pass;
         k_sort_hist<<<nsb, SORT_THREADS, 0, d->st>>>(d->ls_key[cur], M2, shift, d->ls_hist, nsb);
-        k_sort_scan<<<1, 1024, 0, d->st>>>(d->ls_hist, 256 * nsb);
+        const int total = 256 * nsb, per = (total + 1023) / 1024;
+        if (per <= SCAN_SMEM_MAX_PER) k_sort_scan_smem<<<1, 1024, sizeof(unsigned) * 1024 * (size_t)(per | 1), d->st>>>(d->ls_hist, total, per);
+        else k_sort_scan<<<1, 1024, 0, d->st>>>(d->ls_hist, total);
         k_sort_scatter<<<nsb, SORT_THREADS, 0, d->st>>>(d->ls_key[cur], d->ls_idx[cur], M2, shift, d->ls_hist, nsb,
                                                         d->ls_key[cur ^ 1], d->ls_idx[cur ^ 1]);
         cur ^= 1;
