@@ -277,12 +277,123 @@ __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + j
 #define SN_DESC_MAX 64          // supernode descriptors cached in shared memory (else read from global)
 __shared__ int4 s_desc[2 * SN_DESC_MAX];   // {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
 __device__ __forceinline__ int4 sn_desc(const BatchPlan &P, int s, int which) { return P.nsuper <= SN_DESC_MAX ? s_desc[2 * s + which] : P.sn_desc[2 * s + which]; }
+// ---- fronts of order N < 32 (rows k+1 .. N of a column pair sit in one warp).  The owners keep three 32-bit
+// shared-memory addresses per entry (the entry, ucol[i], ucol[j]); the four scratch columns are SN_W doubles apart,
+// so every load of the update is `ld.shared.f64 [reg + immediate]` with no address arithmetic, the activity test
+// (j > k) is one compare of addresses and the store is predicated.
+#define SN_W 34
+__device__ __forceinline__ unsigned b_saddr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+template <int OFF> __device__ __forceinline__ double b_lds(unsigned a)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(a), "n"(OFF));
+    return v;
+}
+__device__ __forceinline__ void b_sts_if(unsigned a, double v, bool p)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.shared.f64 [%0], %1; }" :: "r"(a), "d"(v), "r"((unsigned)p) : "memory");
+}
+__device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double *L, double *xs, double *ucol, const int4 d0, const int4 d1)
+{
+    const int tid = threadIdx.x;
+    const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
+    const int2 *emap = P.Emap2 + d1.y;
+    const int ne = d1.z, ept = (ne + BNT - 1) / BNT;
+    double *lcol = ucol + SN_W, *u1c = ucol + 2 * SN_W, *l1c = ucol + 3 * SN_W;
+    const unsigned Ls = b_saddr(L), xss = b_saddr(xs), uc = b_saddr(ucol);
+    unsigned ea[SN_EPT], pu[SN_EPT], pl[SN_EPT];
+#pragma unroll
+    for (int e = 0; e < SN_EPT; e++) {
+        ea[e] = Ls; pu[e] = uc; pl[e] = uc;                    // j = 0: never active
+        const int idx = tid + e * BNT;
+        if (e < ept && idx < ne) {
+            const int2 em = emap[idx];                          // i | j << 8, position in L (>= 0) or ~index into xs
+            ea[e] = em.y >= 0 ? Ls + 8u * (unsigned)em.y : xss + 8u * (unsigned)(~em.y);
+            pu[e] = uc + 8u * (unsigned)(em.x & 255); pl[e] = uc + 8u * (unsigned)(em.x >> 8);
+        }
+    }
+    int k = 0;
+    while (k < nc) {
+        const int pc = sn_col(base, k, N);
+#ifndef B_NO_PAIRS
+        if (k + 1 < nc) {
+            // two pivots per barrier pair: the lanes of warp 0 scale column k, apply its update to column k+1
+            // (and to the pivot d_{k+1}, redundantly in every lane) and scale column k+1 right away; the
+            // owners then apply both rank-1 updates.  Per entry the same fma's in the same order.
+            const int pc1 = sn_col(base, k + 1, N);
+            if (tid < N - k) {
+                const unsigned mask = 0xffffffffu >> (32 - (N - k));
+                const int i = k + 1 + tid;
+                double *pa0 = (i < N) ? L + pc + i : xs + f + k;
+                double *pa1 = (i < N) ? L + pc1 + i : xs + f + k + 1;          // lane 0: the pivot d_{k+1} itself
+                const double u0 = *pa0, dk = L[pc + k], w = L[pc + k + 1], a1 = *pa1, d1raw = L[pc1 + k + 1];
+                const double rk = __drcp_rn(dk);
+                const double l0 = b_div(u0, dk, rk), lw = b_div(w, dk, rk);
+                const double t1 = fma(-u0, lw, a1), d1v = fma(-w, lw, d1raw);
+                const double r1 = __drcp_rn(d1v);
+                const double l1 = b_div(t1, d1v, r1);
+                __syncwarp(mask);                               // every lane has read w before lane 0 overwrites it
+                ucol[i] = u0; lcol[i] = l0; *pa0 = l0;
+                if (tid == 0) *pa1 = d1v;
+                else { u1c[i] = t1; l1c[i] = l1; *pa1 = l1; }
+            }
+            __syncthreads();
+            const unsigned thr = uc + 8u * (unsigned)(k + 1);
+#pragma unroll
+            for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
+                if (h < ept) {
+                    double u0v[SN_EPT / 2], l0v[SN_EPT / 2], u1v[SN_EPT / 2], l1v[SN_EPT / 2], av[SN_EPT / 2];
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) {
+                        u0v[e] = b_lds<0>(pu[h + e]); l0v[e] = b_lds<8 * SN_W>(pl[h + e]);
+                        u1v[e] = b_lds<16 * SN_W>(pu[h + e]); l1v[e] = b_lds<24 * SN_W>(pl[h + e]);
+                        av[e] = b_lds<0>(ea[h + e]);
+                    }
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
+#pragma unroll
+                    for (int e = 0; e < SN_EPT / 2; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
+                }
+            }
+            __syncthreads();
+            k += 2;
+            continue;
+        }
+#endif
+        if (tid < N - k) {                                  // rows k+1 .. N (N = right-hand side)
+            const int i = k + 1 + tid;
+            double *pa = (i < N) ? L + pc + i : xs + f + k;
+            const double u = *pa, dk = L[pc + k];
+            const double l = b_div(u, dk, __drcp_rn(dk));
+            ucol[i] = u; lcol[i] = l; *pa = l;
+        }
+        __syncthreads();
+        const unsigned thr = uc + 8u * (unsigned)k;
+#pragma unroll
+        for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
+            if (h < ept) {
+                double uv[SN_EPT / 2], lv[SN_EPT / 2], av[SN_EPT / 2];
+#pragma unroll
+                for (int e = 0; e < SN_EPT / 2; e++) { uv[e] = b_lds<0>(pu[h + e]); lv[e] = b_lds<8 * SN_W>(pl[h + e]); av[e] = b_lds<0>(ea[h + e]); }
+#pragma unroll
+                for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-uv[e], lv[e], av[e]);
+#pragma unroll
+                for (int e = 0; e < SN_EPT / 2; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
+            }
+        }
+        __syncthreads();
+        k++;
+    }
+}
 __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
     const int tid = threadIdx.x;
     for (int s = 0; s < P.nsuper; s++) {
         const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
         const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
+        if (N < 32) { b_factor_front_small(P, L, xs, ucol, d0, d1); continue; }
         const int2 *emap = P.Emap2 + d1.y;
         const int ne = d1.z, ept = (ne + BNT - 1) / BNT;
         double *lcol = ucol + N + 1;
@@ -298,11 +409,7 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
                 ea[e] = em.y >= 0 ? L + em.y : xs + ~em.y;
             }
         }
-#ifdef B_NO_PAIRS
-        const bool pairs = false;
-#else
-        const bool pairs = N < 32;                              // rows k+1 .. N of a column pair sit in one warp
-#endif
+        const bool pairs = false;                               // fronts of order < 32 take b_factor_front_small
         double *u1c = ucol + 2 * (N + 1), *l1c = ucol + 3 * (N + 1);
         int k = 0;
         while (k < nc) {
@@ -1228,7 +1335,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK;
         P.nKpack = mode == 1 ? b->lnz : n * (n + 1) / 2;
         P.nKround = P_nKround;
-        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = max_front + 2;
+        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = std::max(max_front + 2, SN_W);
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
