@@ -51,6 +51,7 @@ struct BatchPlan {
     int nKround;                             // K assembly: rounds of BNT entries
     const int2 *Kround, *Kmeta;
     const uint2 *Ktr;
+    const unsigned *Ktr32;                   // same program in 4-byte records when m < 1023 and nnz(A) <= 2048, else null
     const int *Lcp, *Lri;                    // L column patterns (rows strictly below the diagonal)
     const int *Lrp, *Lci;                    // L row patterns (columns strictly left of the diagonal)
     // supernodal register path (mode 1): every front fits one warp (N + 1 <= 32 lanes)
@@ -59,7 +60,7 @@ struct BatchPlan {
     const int *sn_base;                      // offset of the packed trapezoid of each supernode in the L area
     const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
     const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
-    int max_front, ucolw;
+    int max_front, ucolw, nSrow;
     const int2 *Emap2;                       // owned entries of each front: {i | j << 8, position in L or ~index into xs}, column major, j >= 1, i = j..N
     const int4 *sn_desc;                     // per supernode {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
     // settings (reference include/types.h:96-116)
@@ -201,12 +202,21 @@ __device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av,
     // and the slot loop has a uniform trip count (loads of several slots in flight)
     for (int r = 0; r < P.nKround; r++) {
         const int2 rk = P.Kround[r];                          // first slot, slots
-        const uint2 *T = P.Ktr + (size_t)rk.x * BNT + threadIdx.x;
         double v = 0.0;
+        if (P.Ktr32) {                                        // small problems: 4-byte records row | a1 << 10 | a2 << 21
+            const unsigned *T = P.Ktr32 + (size_t)rk.x * BNT + threadIdx.x;
 #pragma unroll (kKUnroll)
-        for (int k = 0; k < rk.y; k++) {
-            const uint2 w = T[(size_t)k * BNT];               // row (or -1: padding), a1 | a2 << 16
-            if ((int)w.x >= 0) v = fma(om[w.x], Av[w.y & 0xffffu] * Av[w.y >> 16], v);
+            for (int k = 0; k < rk.y; k++) {
+                const unsigned w = T[(size_t)k * BNT];
+                if (w != 0xffffffffu) v = fma(om[w & 1023u], Av[(w >> 10) & 2047u] * Av[w >> 21], v);
+            }
+        } else {
+            const uint2 *T = P.Ktr + (size_t)rk.x * BNT + threadIdx.x;
+#pragma unroll (kKUnroll)
+            for (int k = 0; k < rk.y; k++) {
+                const uint2 w = T[(size_t)k * BNT];           // row (or -1: padding), a1 | a2 << 16
+                if ((int)w.x >= 0) v = fma(om[w.x], Av[w.y & 0xffffu] * Av[w.y >> 16], v);
+            }
         }
         const int e = r * BNT + threadIdx.x;
         if (e < P.nnzK) {
@@ -276,6 +286,8 @@ __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + j
 #define SN_EPT 8
 #define SN_DESC_MAX 64          // supernode descriptors cached in shared memory (else read from global)
 __shared__ int4 s_desc[2 * SN_DESC_MAX];   // {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
+#define SN_ROWS_MAX 512         // rows below the pivot blocks (all supernodes) cached in shared memory
+__shared__ int s_rows[SN_ROWS_MAX];
 __device__ __forceinline__ int4 sn_desc(const BatchPlan &P, int s, int which) { return P.nsuper <= SN_DESC_MAX ? s_desc[2 * s + which] : P.sn_desc[2 * s + which]; }
 // ---- fronts of order N < 32 (rows k+1 .. N of a column pair sit in one warp).  The owners keep three 32-bit
 // shared-memory addresses per entry (the entry, ucol[i], ucol[j]); the four scratch columns are SN_W doubles apart,
@@ -497,13 +509,13 @@ __device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, 
     for (int s = P.nsuper - 1; s >= 0; s--) {
         const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
         const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
-        const int *rows = P.Srow + d1.x;
+        const int *rows = (P.nSrow <= SN_ROWS_MAX ? s_rows : P.Srow) + d1.x;
         const int mycol = sn_col(base, lane, N);
+        double v = 0.0;
+        if (lane < nc) v = xs[f + lane]; else if (lane < N) v = xs[rows[lane - nc]];
         double col[SN_NMAX];
 #pragma unroll
         for (int i = 1; i < SN_NMAX; i++) col[i] = (i < N && lane < nc && lane < i) ? L[mycol + i] : 0.0;
-        double v = 0.0;
-        if (lane < nc) v = xs[f + lane]; else if (lane < N) v = xs[rows[lane - nc]];
 #pragma unroll
         for (int i = SN_NMAX - 1; i >= 1; i--) {
             if (i < N) {
@@ -1077,6 +1089,7 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const BatchPlan 
     V.ucol = p; p += 4 * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
     if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
+    if (P.nSrow <= SN_ROWS_MAX) for (int t = threadIdx.x; t < P.nSrow; t += BNT) s_rows[t] = P.Srow[t];
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) s_b = atomicAdd(io.next, 1);
@@ -1335,13 +1348,21 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.n = n; P.m = m; P.nnzA = nnzA; P.nnzQ = nnzQ; P.nnzK = nnzK;
         P.nKpack = mode == 1 ? b->lnz : n * (n + 1) / 2;
         P.nKround = P_nKround;
-        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = std::max(max_front + 2, SN_W);
+        P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = std::max(max_front + 2, SN_W); P.nSrow = (int)Srow.size();
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
         P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
         P.ellA.nround = (int)ellRound[0].size(); P.ellAt.nround = (int)ellRound[1].size(); P.ellQ.nround = (int)ellRound[2].size();
         if (b_upload(b, &P.ellA.round, ellRound[0]) || b_upload(b, &P.ellA.rec, ellRec[0]) || b_upload(b, &P.ellAt.round, ellRound[1]) ||
             b_upload(b, &P.ellAt.rec, ellRec[1]) || b_upload(b, &P.ellQ.round, ellRound[2]) || b_upload(b, &P.ellQ.rec, ellRec[2])) break;
+#ifndef B_NO_KTR32
+        if (m < 1023 && nnzA <= 2048) {
+            std::vector<unsigned> Ktr32(Ktr.size());
+            for (size_t t = 0; t < Ktr.size(); t++)
+                Ktr32[t] = (int)Ktr[t].x < 0 ? 0xffffffffu : (Ktr[t].x | ((Ktr[t].y & 0xffffu) << 10) | ((Ktr[t].y >> 16) << 21));
+            if (b_upload(b, &P.Ktr32, Ktr32)) break;
+        }
+#endif
         if (b_upload(b, &P.Ap, vAp) || b_upload(b, &P.Ai, vAi) || b_upload(b, &P.Rp, Rp) || b_upload(b, &P.Rj, Rj) || b_upload(b, &P.Rsrc, Rsrc) ||
             b_upload(b, &P.Qp, vQp) || b_upload(b, &P.Qi, vQi) || b_upload(b, &P.Fp, Fp) || b_upload(b, &P.Fj, Fj) || b_upload(b, &P.Fsrc, Fsrc) ||
             b_upload(b, &P.Fdiag, Fdiag) || b_upload(b, &P.perm, perm) || b_upload(b, &P.Kround, Kround) || b_upload(b, &P.Kmeta, Kmeta) || b_upload(b, &P.Ktr, Ktr) ||
