@@ -31,6 +31,12 @@
 #define B_KUNROLL 4            // K assembly: product records in flight per thread
 #endif
 constexpr int kKUnroll = B_KUNROLL;
+#ifdef B_NOINLINE
+#define B_FN __noinline__
+#else
+#define B_FN __forceinline__   // no address of the kernel parameter struct is ever taken: plan fields stay in the constant bank
+#endif
+#define B_GC __grid_constant__
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
 
@@ -399,7 +405,7 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
         k++;
     }
 }
-__device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
+__device__ B_FN void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
     const int tid = threadIdx.x;
     for (int s = 0; s < P.nsuper; s++) {
@@ -503,7 +509,7 @@ __device__ __noinline__ void b_factor_fronts(const BatchPlan &P, double *L, doub
 }
 // x = L^{-T} xs: lane c owns pivot column c of the front, lanes nc..N-1 carry the already final
 // entries of the rows below; same fma sequence per entry as b_backward (descending row order)
-__device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, double *xs)
+__device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *xs)
 {
     const int lane = threadIdx.x & 31;
     for (int s = P.nsuper - 1; s >= 0; s--) {
@@ -529,7 +535,7 @@ __device__ __noinline__ void b_backward_sn(const BatchPlan &P, const double *L, 
 }
 
 // generic variant (fronts wider than a warp): one warp, column-parallel scatter per front row
-__device__ __noinline__ void b_backward_fronts(const BatchPlan &P, const double *L, double *xs)
+__device__ B_FN void b_backward_fronts(const BatchPlan &P, const double *L, double *xs)
 {
     const int lane = threadIdx.x & 31;
     for (int s = P.nsuper - 1; s >= 0; s--) {
@@ -560,7 +566,7 @@ __device__ __forceinline__ void b_ls_contrib(const double *delta, const double *
     if (d > 0.0) { da = d * d; db = -(d * al); }
     else { da = -(d * d); db = d * al; }
 }
-__device__ double b_linesearch(const BatchPlan &P, const BVec &V)
+__device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V)
 {
     const int tid = threadIdx.x, n = P.n, m = P.m, M2 = 2 * m, P2 = P.P2, lane = tid & 31, wid = tid >> 5;
     double *delta = V.K, *alpha = V.K + M2;
@@ -755,7 +761,7 @@ __device__ double b_linesearch(const BatchPlan &P, const BVec &V)
 #define FOR_M(i) for (int i = threadIdx.x; i < m; i += BNT)
 
 #define B_TICK(slot) if (io.timing) { const long long now_ = clock64(); tacc[slot] += now_ - tlast; tlast = now_; }
-__device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BVec &V, const int b)
+__device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BVec &V, const int b)
 {
     const int n = P.n, m = P.m, tid = threadIdx.x;
     const bool scaled = P.scaling > 0, proximal = P.proximal != 0;
@@ -1070,7 +1076,7 @@ __device__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BV
 }
 
 // ------------------------------------------------------------------------------- kernel
-__global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const BatchPlan P, const BatchIO io)
+__global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC BatchPlan P, const B_GC BatchIO io)
 {
     extern __shared__ double sm[];
     __shared__ int s_b;
