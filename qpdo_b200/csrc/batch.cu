@@ -44,6 +44,9 @@ constexpr int kKUnroll = B_KUNROLL;
 // round slot-major (a warp reads 32 consecutive 4-byte records per slot; uniform trip count, several loads in
 // flight); record = value index | column << 16 | second-half flag << 31, 0xffffffff = padding
 struct BatchEll { int nround; const int2 *round; const unsigned *rec; };
+#define B_ROUNDS_MAX 8          // round tables of up to this many rounds are cached in shared memory
+__shared__ int2 s_round[4][B_ROUNDS_MAX];      // ellA, ellAt, ellQ, K assembly
+__device__ __forceinline__ int2 b_round(int which, int nround, const int2 *tab, int r) { return nround <= B_ROUNDS_MAX ? s_round[which][r] : tab[r]; }
 
 struct BatchPlan {
     int n, m, nnzA, nnzQ, nnzK, nKpack, karea, P2;
@@ -144,7 +147,7 @@ __device__ __forceinline__ double bclamp(double a, double lo, double hi)
 __device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, const double *x, double *y)
 {   // CSR gather in ascending column order == CSC scatter order (t_cholmod_sdmult.c:297-320)
     for (int r = 0; r < P.ellA.nround; r++) {
-        const int2 rk = P.ellA.round[r];
+        const int2 rk = b_round(0, P.ellA.nround, P.ellA.round, r);
         const unsigned *T = P.ellA.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
 #pragma unroll 4
@@ -156,7 +159,7 @@ __device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, c
 __device__ __forceinline__ void b_spmv_At(const BatchPlan &P, const double *Av, const double *x, double *y)
 {   // t_cholmod_sdmult.c:141-165
     for (int r = 0; r < P.ellAt.nround; r++) {
-        const int2 rk = P.ellAt.round[r];
+        const int2 rk = b_round(1, P.ellAt.nround, P.ellAt.round, r);
         const unsigned *T = P.ellAt.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
 #pragma unroll 4
@@ -168,7 +171,7 @@ __device__ __forceinline__ void b_spmv_At(const BatchPlan &P, const double *Av, 
 __device__ __forceinline__ void b_spmv_Q(const BatchPlan &P, const double *Qv, const double *x, double *y)
 {   // t_cholmod_sdmult.c:440-484 (split sum: the terms of the lower-triangular columns, then the mirrored ones)
     for (int r = 0; r < P.ellQ.nround; r++) {
-        const int2 rk = P.ellQ.round[r];
+        const int2 rk = b_round(2, P.ellQ.nround, P.ellQ.round, r);
         const unsigned *T = P.ellQ.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s1 = 0.0, s2 = 0.0;
 #pragma unroll 4
@@ -207,7 +210,10 @@ __device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av,
     // the products of round r sit slot-major, so that a warp reads 32 consecutive 8-byte records per slot
     // and the slot loop has a uniform trip count (loads of several slots in flight)
     for (int r = 0; r < P.nKround; r++) {
-        const int2 rk = P.Kround[r];                          // first slot, slots
+        const int2 rk = b_round(3, P.nKround, P.Kround, r);   // first slot, slots
+        const int e = r * BNT + threadIdx.x;
+        int2 mt; mt.x = 0; mt.y = -1;
+        if (e < P.nnzK) mt = P.Kmeta[e];                      // packed position | diagonal flag << 31, index into Q's values or -1 (in flight during the slot loop)
         double v = 0.0;
         if (P.Ktr32) {                                        // small problems: 4-byte records row | a1 << 10 | a2 << 21
             const unsigned *T = P.Ktr32 + (size_t)rk.x * BNT + threadIdx.x;
@@ -224,9 +230,7 @@ __device__ __forceinline__ void b_assemble(const BatchPlan &P, const double *Av,
                 if ((int)w.x >= 0) v = fma(om[w.x], Av[w.y & 0xffffu] * Av[w.y >> 16], v);
             }
         }
-        const int e = r * BNT + threadIdx.x;
         if (e < P.nnzK) {
-            const int2 mt = P.Kmeta[e];                       // packed position | diagonal flag << 31, index into Q's values or -1
             if (mt.y >= 0) v += Qv[mt.y];
             if (P.proximal && mt.x < 0) v += sigma;
             K[mt.x & 0x7fffffff] = v;
@@ -1096,6 +1100,13 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC Batch
     V.act = (unsigned char *)p; V.acto = V.act + m;
     if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
     if (P.nSrow <= SN_ROWS_MAX) for (int t = threadIdx.x; t < P.nSrow; t += BNT) s_rows[t] = P.Srow[t];
+    if (threadIdx.x < B_ROUNDS_MAX) {
+        const int t = threadIdx.x;
+        if (t < P.ellA.nround && P.ellA.nround <= B_ROUNDS_MAX) s_round[0][t] = P.ellA.round[t];
+        if (t < P.ellAt.nround && P.ellAt.nround <= B_ROUNDS_MAX) s_round[1][t] = P.ellAt.round[t];
+        if (t < P.ellQ.nround && P.ellQ.nround <= B_ROUNDS_MAX) s_round[2][t] = P.ellQ.round[t];
+        if (t < P.nKround && P.nKround <= B_ROUNDS_MAX) s_round[3][t] = P.Kround[t];
+    }
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) s_b = atomicAdd(io.next, 1);
