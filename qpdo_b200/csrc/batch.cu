@@ -304,6 +304,7 @@ __device__ __forceinline__ int4 sn_desc(const BatchPlan &P, int s, int which) { 
 // so every load of the update is `ld.shared.f64 [reg + immediate]` with no address arithmetic, the activity test
 // (j > k) is one compare of addresses and the store is predicated.
 #define SN_W 34
+#define SN_EPTS 4             // owned entries per thread of a small front (N (N + 1) / 2 - 1 <= 495 <= 4 * BNT)
 __device__ __forceinline__ unsigned b_saddr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 template <int OFF> __device__ __forceinline__ double b_lds(unsigned a)
 {
@@ -323,9 +324,9 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
     const int ne = d1.z, ept = (ne + BNT - 1) / BNT;
     double *lcol = ucol + SN_W, *u1c = ucol + 2 * SN_W, *l1c = ucol + 3 * SN_W;
     const unsigned Ls = b_saddr(L), xss = b_saddr(xs), uc = b_saddr(ucol);
-    unsigned ea[SN_EPT], pu[SN_EPT], pl[SN_EPT];
+    unsigned ea[SN_EPTS], pu[SN_EPTS], pl[SN_EPTS];       // N < 32: at most 495 owned entries, 4 per thread
 #pragma unroll
-    for (int e = 0; e < SN_EPT; e++) {
+    for (int e = 0; e < SN_EPTS; e++) {
         ea[e] = Ls; pu[e] = uc; pl[e] = uc;                    // j = 0: never active
         const int idx = tid + e * BNT;
         if (e < ept && idx < ne) {
@@ -362,21 +363,21 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
             __syncthreads();
             const unsigned thr = uc + 8u * (unsigned)(k + 1);
 #pragma unroll
-            for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
+            for (int h = 0; h < SN_EPTS; h += SN_EPTS) {
                 if (h < ept) {
-                    double u0v[SN_EPT / 2], l0v[SN_EPT / 2], u1v[SN_EPT / 2], l1v[SN_EPT / 2], av[SN_EPT / 2];
+                    double u0v[SN_EPTS], l0v[SN_EPTS], u1v[SN_EPTS], l1v[SN_EPTS], av[SN_EPTS];
 #pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) {
+                    for (int e = 0; e < SN_EPTS; e++) {
                         u0v[e] = b_lds<0>(pu[h + e]); l0v[e] = b_lds<8 * SN_W>(pl[h + e]);
                         u1v[e] = b_lds<16 * SN_W>(pu[h + e]); l1v[e] = b_lds<24 * SN_W>(pl[h + e]);
                         av[e] = b_lds<0>(ea[h + e]);
                     }
 #pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
+                    for (int e = 0; e < SN_EPTS; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
 #pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
+                    for (int e = 0; e < SN_EPTS; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
 #pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
+                    for (int e = 0; e < SN_EPTS; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
                 }
             }
             __syncthreads();
@@ -394,15 +395,15 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
         __syncthreads();
         const unsigned thr = uc + 8u * (unsigned)k;
 #pragma unroll
-        for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
+        for (int h = 0; h < SN_EPTS; h += SN_EPTS) {
             if (h < ept) {
-                double uv[SN_EPT / 2], lv[SN_EPT / 2], av[SN_EPT / 2];
+                double uv[SN_EPTS], lv[SN_EPTS], av[SN_EPTS];
 #pragma unroll
-                for (int e = 0; e < SN_EPT / 2; e++) { uv[e] = b_lds<0>(pu[h + e]); lv[e] = b_lds<8 * SN_W>(pl[h + e]); av[e] = b_lds<0>(ea[h + e]); }
+                for (int e = 0; e < SN_EPTS; e++) { uv[e] = b_lds<0>(pu[h + e]); lv[e] = b_lds<8 * SN_W>(pl[h + e]); av[e] = b_lds<0>(ea[h + e]); }
 #pragma unroll
-                for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-uv[e], lv[e], av[e]);
+                for (int e = 0; e < SN_EPTS; e++) av[e] = fma(-uv[e], lv[e], av[e]);
 #pragma unroll
-                for (int e = 0; e < SN_EPT / 2; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
+                for (int e = 0; e < SN_EPTS; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
             }
         }
         __syncthreads();
@@ -570,7 +571,7 @@ __device__ __forceinline__ void b_ls_contrib(const double *delta, const double *
     if (d > 0.0) { da = d * d; db = -(d * al); }
     else { da = -(d * d); db = d * al; }
 }
-__device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V)
+template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V)
 {
     const int tid = threadIdx.x, n = P.n, m = P.m, M2 = 2 * m, P2 = P.P2, lane = tid & 31, wid = tid >> 5;
     double *delta = V.K, *alpha = V.K + M2;
@@ -611,7 +612,6 @@ __device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V
     // the breakpoints with t > 0 are compacted to the front of key / idx (ballot prefix sums), so that the
     // bitonic network only spans next_pow2(nL) slots instead of next_pow2(2m); (key, idx) is a total order,
     // the sorted prefix does not depend on where the pairs started
-    constexpr int RLMAX = 8;
     const bool compact = P2 <= RLMAX * BNT;
     __shared__ int cw[RLMAX * BNW];
     unsigned long long kreg[RLMAX];
@@ -1051,7 +1051,8 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
             __syncthreads();
             B_TICK(6)
-            tau = b_linesearch(P, V);
+            // breakpoint passes unrolled to what 2m needs (the unrolled code of unused passes costs instruction fetch)
+            tau = P.P2 <= 2 * BNT ? b_linesearch<2>(P, V) : P.P2 <= 4 * BNT ? b_linesearch<4>(P, V) : b_linesearch<8>(P, V);
             FOR_N(i) { V.x[i] = V.x[i] + tau * V.dx[i]; V.Qx[i] = V.Qx[i] + tau * V.Qdx[i]; V.Aty[i] = V.Aty[i] + tau * V.Atdy[i]; }
             FOR_M(i) { V.y[i] = V.y[i] + tau * V.dy[i]; V.Ax[i] = V.Ax[i] + tau * V.Adx[i]; }
             __syncthreads();

@@ -150,6 +150,30 @@ def test_batch_random_dense_family_and_more_instances_than_ctas(oracle_mod):
 
 
 @pytest.mark.gpu
+def test_batch_wide_product_records_and_generic_front(oracle_mod):
+    """nnz(A) > 2048 takes the 8-byte K-assembly records (the 4-byte form needs m < 1023, nnz(A) <= 2048) and
+    a dense 60 x 60 K is one front of order 60 > 31: generic front factorization and backward solve"""
+    n, m = 60, 70
+    p0 = problems.random_qp(n, m, 0.9, seed=77)
+    Q = sp.tril(sp.csc_matrix(p0["Q"]), format="csc"); Q.sort_indices()
+    A = sp.csc_matrix(p0["A"]); A.sort_indices()
+    assert A.nnz > 2048
+    B = 48
+    rng = np.random.default_rng(9)
+    Qx = np.tile(Q.data, (B, 1)); Ax = np.tile(A.data, (B, 1)) * (1 + 0.05 * rng.uniform(-1, 1, (B, A.nnz)))
+    q = p0["q"] + 0.3 * rng.standard_normal((B, n)); l = np.tile(p0["l"], (B, 1)); u = np.tile(p0["u"], (B, 1))
+    bt = qbatch.Batch(n, m, Q.indptr, Q.indices, A.indptr, A.indices, B, {})
+    x, y, summ, act = bt.solve(Qx, Ax, q, l, u)
+    bt.destroy()
+    for i in range(0, B, 6):
+        p = dict(Q=sp.csc_matrix((Qx[i], Q.indices, Q.indptr), shape=(n, n)), q=q[i],
+                 A=sp.csc_matrix((Ax[i], A.indices, A.indptr), shape=(m, n)), l=l[i], u=u[i])
+        p["Q"] = p["Q"] + sp.tril(p["Q"], -1).T
+        o = oracle_mod.solve(p, {}, trace=False)
+        _check_instance("wide %d" % i, o, x[i], y[i], summ[i], act[i])
+
+
+@pytest.mark.gpu
 def test_batch_solve_data_entry_with_reference_structs(oracle_mod):
     """qpdo_batch_solve_data: arrays of the reference's own QPDOData (include/types.h:81-90)"""
     import qpdo_b200
