@@ -144,29 +144,33 @@ __device__ __forceinline__ double bclamp(double a, double lo, double hi)
 }
 
 // ------------------------------------------------------------------------------- SpMV (cholmod_sdmult order)
-__device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, const double *x, double *y)
-{   // CSR gather in ascending column order == CSC scatter order (t_cholmod_sdmult.c:297-320)
-    for (int r = 0; r < P.ellA.nround; r++) {
-        const int2 rk = b_round(0, P.ellA.nround, P.ellA.round, r);
-        const unsigned *T = P.ellA.rec + (size_t)rk.x * BNT + threadIdx.x;
+// one out-of-line copy serves every y = A x and y = A' x of the loop (the inlined copies at seven call sites were
+// a fifth of the instructions fetched per Newton step); everything it needs comes in registers
+#ifdef B_SPMV_INLINE
+#define B_SPMV_FN __forceinline__
+#else
+#define B_SPMV_FN __noinline__
+#endif
+__device__ B_SPMV_FN void b_ell_gather(int which, int nround, const int2 *round, const unsigned *rec, int nrows,
+                                       const double *val, const double *x, double *y)
+{
+    for (int r = 0; r < nround; r++) {
+        const int2 rk = b_round(which, nround, round, r);
+        const unsigned *T = rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
 #pragma unroll 4
-        for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += Av[w & 0xffffu] * x[w >> 16]; }
+        for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += val[w & 0xffffu] * x[w >> 16]; }
         const int i = r * BNT + threadIdx.x;
-        if (i < P.m) y[i] = s;
+        if (i < nrows) y[i] = s;
     }
+}
+__device__ __forceinline__ void b_spmv_A(const BatchPlan &P, const double *Av, const double *x, double *y)
+{   // CSR gather in ascending column order == CSC scatter order (t_cholmod_sdmult.c:297-320)
+    b_ell_gather(0, P.ellA.nround, P.ellA.round, P.ellA.rec, P.m, Av, x, y);
 }
 __device__ __forceinline__ void b_spmv_At(const BatchPlan &P, const double *Av, const double *x, double *y)
 {   // t_cholmod_sdmult.c:141-165
-    for (int r = 0; r < P.ellAt.nround; r++) {
-        const int2 rk = b_round(1, P.ellAt.nround, P.ellAt.round, r);
-        const unsigned *T = P.ellAt.rec + (size_t)rk.x * BNT + threadIdx.x;
-        double s = 0.0;
-#pragma unroll 4
-        for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += Av[w & 0xffffu] * x[w >> 16]; }
-        const int j = r * BNT + threadIdx.x;
-        if (j < P.n) y[j] = s;
-    }
+    b_ell_gather(1, P.ellAt.nround, P.ellAt.round, P.ellAt.rec, P.n, Av, x, y);
 }
 __device__ __forceinline__ void b_spmv_Q(const BatchPlan &P, const double *Qv, const double *x, double *y)
 {   // t_cholmod_sdmult.c:440-484 (split sum: the terms of the lower-triangular columns, then the mirrored ones)
