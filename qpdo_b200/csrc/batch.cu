@@ -91,9 +91,20 @@ struct BatchIO {
 template <int K> __device__ __forceinline__ void block_max(double (&v)[K], double *red)
 {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // every caller reduces absolute values accumulated with `t > v ? t : v` (never negative, never NaN): their
+    // IEEE bit patterns order like unsigned integers, so the warp maximum is two 32-bit redux.sync.max (high
+    // word, then the low word among the lanes that hold the maximal high word) instead of five shuffle rounds
 #pragma unroll
-    for (int k = 0; k < K; k++)
+    for (int k = 0; k < K; k++) {
+#ifdef B_SHFL_MAX
         for (int o = 16; o; o >>= 1) { double t = __shfl_xor_sync(0xffffffffu, v[k], o); v[k] = t > v[k] ? t : v[k]; }
+#else
+        const unsigned hi = (unsigned)__double2hiint(v[k]), lo = (unsigned)__double2loint(v[k]);
+        const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+        const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+        v[k] = __hiloint2double((int)mh, (int)ml);
+#endif
+    }
     __syncthreads();
     if (lane == 0)
 #pragma unroll
