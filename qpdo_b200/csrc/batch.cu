@@ -1016,10 +1016,14 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                 V.act[i] = (unsigned char)a;
                 ca += a; ce += (a && !o); cl += (!a && o);
             }
-            {
-                double cs[3] = {(double)ca, (double)ce, (double)cl};
-                block_sum<3>(cs, red);
-                n_active = (int)(cs[0] + 0.5); n_enter = (int)(cs[1] + 0.5); n_leave = (int)(cs[2] + 0.5);
+            {   // integer counts: one redux.sync.add per count inside the warp, warp partials through shared memory
+                const int wa_ = __reduce_add_sync(0xffffffffu, ca), we_ = __reduce_add_sync(0xffffffffu, ce), wl_ = __reduce_add_sync(0xffffffffu, cl);
+                int *ri = (int *)red;
+                __syncthreads();
+                if ((tid & 31) == 0) { ri[(tid >> 5) * 3] = wa_; ri[(tid >> 5) * 3 + 1] = we_; ri[(tid >> 5) * 3 + 2] = wl_; }
+                __syncthreads();
+                n_active = n_enter = n_leave = 0;
+                for (int w = 0; w < BNW; w++) { n_active += ri[w * 3]; n_enter += ri[w * 3 + 1]; n_leave += ri[w * 3 + 2]; }
             }
             int mode;
             if ((reset_newton && n_active) || (n_enter + n_leave) > QPDO_MAX_RANK_UPDATE) { mode = 0; reset_newton = 0; }
