@@ -235,7 +235,7 @@ from qpdo_b200 import batch as qbatch      # ctypes mirror of include/qpdo_batch
 import ctypes as C
 
 C5_BATCH = 65536
-TRAFFIC_PER_QP_NCU = 12062          # measured DRAM bytes per QP (26.55 MB read + 2.01 MB written for 2,368 QPs)
+TRAFFIC_PER_QP_NCU = 11256          # measured DRAM bytes per QP (26.62 MB read + 0.04 MB written back inside the launch, 2,368 QPs; results reach DRAM after the launch)
 
 
 def algorithmic_bytes_per_qp(n, m, nnzQ, nnzA):
