@@ -37,6 +37,14 @@ constexpr int kKUnroll = B_KUNROLL;
 #define B_FN __forceinline__   // no address of the kernel parameter struct is ever taken: plan fields stay in the constant bank
 #endif
 #define B_GC __grid_constant__
+// instance data streams through once: evict-first loads / stores keep the shared index tables in the 23 KB of L1
+#ifdef B_NO_STREAM
+#define B_LDS_IN(p) (*(p))
+#define B_STS_OUT(p, v) (*(p) = (v))
+#else
+#define B_LDS_IN(p) __ldcs(p)
+#define B_STS_OUT(p, v) __stcs((p), (v))
+#endif
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
 
@@ -787,11 +795,11 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
     double *red = V.red;
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = io.timing ? clock64() : 0;     // setup, residuals+outer, newton prep, assemble, factor, backward, direction, linesearch+update
     // ---- load (qpdo_setup's deep copy, src/qpdo.c:100-109); infinite bounds clipped like qpdo.m:138-139
-    for (int k = tid; k < P.nnzA; k += BNT) V.Av[k] = io.Ax[(size_t)b * P.nnzA + k];
-    for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = io.Qx[(size_t)b * P.nnzQ + k];
-    FOR_N(i) { V.q[i] = io.q[(size_t)b * n + i]; V.x[i] = 0.0; V.xbar[i] = 0.0; V.Qx[i] = 0.0; V.Aty[i] = 0.0; V.D[i] = 1.0; V.dx[i] = 0.0; }
+    for (int k = tid; k < P.nnzA; k += BNT) V.Av[k] = B_LDS_IN(io.Ax + (size_t)b * P.nnzA + k);
+    for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = B_LDS_IN(io.Qx + (size_t)b * P.nnzQ + k);
+    FOR_N(i) { V.q[i] = B_LDS_IN(io.q + (size_t)b * n + i); V.x[i] = 0.0; V.xbar[i] = 0.0; V.Qx[i] = 0.0; V.Aty[i] = 0.0; V.D[i] = 1.0; V.dx[i] = 0.0; }
     FOR_M(i) {
-        double lo = io.l[(size_t)b * m + i], hi = io.u[(size_t)b * m + i];
+        double lo = B_LDS_IN(io.l + (size_t)b * m + i), hi = B_LDS_IN(io.u + (size_t)b * m + i);
         V.l[i] = lo > -B_INFTY ? lo : -B_INFTY; V.u[i] = hi < B_INFTY ? hi : B_INFTY;
         V.y[i] = 0.0; V.ybar[i] = 0.0; V.Ax[i] = 0.0; V.E[i] = 1.0; V.om[i] = 0.0; V.dy[i] = 0.0; V.rpo[i] = 0.0;
         V.act[i] = 0; V.acto[i] = 0;
@@ -1087,8 +1095,8 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
     double objective = ob[0];
     if (scaled) objective = objective * cinv;
     objective = objective + (io.c ? io.c[b] : 0.0);
-    if (io.x) { FOR_N(i) io.x[(size_t)b * n + i] = scaled ? V.x[i] * V.D[i] : V.x[i]; }
-    if (io.y) { FOR_M(i) { double v = V.y[i]; if (scaled) { v = v * cinv; v = v * V.E[i]; } io.y[(size_t)b * m + i] = v; } }
+    if (io.x) { FOR_N(i) B_STS_OUT(io.x + (size_t)b * n + i, scaled ? V.x[i] * V.D[i] : V.x[i]); }
+    if (io.y) { FOR_M(i) { double v = V.y[i]; if (scaled) { v = v * cinv; v = v * V.E[i]; } B_STS_OUT(io.y + (size_t)b * m + i, v); } }
     if (io.active) { FOR_M(i) io.active[(size_t)b * m + i] = V.act[i]; }
     if (io.timing && tid == 0) { B_TICK(1) for (int j = 0; j < 8; j++) io.timing[(size_t)b * 8 + j] = tacc[j]; }
     if (io.summary && tid == 0) {
