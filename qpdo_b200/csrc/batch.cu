@@ -455,56 +455,10 @@ __device__ B_FN void b_factor_fronts(const BatchPlan &P, double *L, double *xs, 
                 ea[e] = em.y >= 0 ? L + em.y : xs + ~em.y;
             }
         }
-        const bool pairs = false;                               // fronts of order < 32 take b_factor_front_small
-        double *u1c = ucol + 2 * (N + 1), *l1c = ucol + 3 * (N + 1);
+        // one pivot per barrier pair here; fronts of order < 32 took b_factor_front_small (two pivots per pair)
         int k = 0;
         while (k < nc) {
             const int pc = sn_col(base, k, N);
-            if (pairs && k + 1 < nc) {
-                // two pivots per barrier pair: the lanes of warp 0 scale column k, apply its update to column k+1
-                // (and to the pivot d_{k+1}, redundantly in every lane) and scale column k+1 right away; the
-                // owners then apply both rank-1 updates.  Per entry the same fma's in the same order.
-                const int pc1 = sn_col(base, k + 1, N);
-                if (tid < N - k) {
-                    const unsigned mask = 0xffffffffu >> (32 - (N - k));
-                    const int i = k + 1 + tid;
-                    double *pa0 = (i < N) ? L + pc + i : xs + f + k;
-                    double *pa1 = (i < N) ? L + pc1 + i : xs + f + k + 1;          // lane 0: the pivot d_{k+1} itself
-                    const double u0 = *pa0, dk = L[pc + k], w = L[pc + k + 1], a1 = *pa1, d1raw = L[pc1 + k + 1];
-                    const double rk = __drcp_rn(dk);
-                    const double l0 = b_div(u0, dk, rk), lw = b_div(w, dk, rk);
-                    const double t1 = fma(-u0, lw, a1), d1 = fma(-w, lw, d1raw);
-                    const double r1 = __drcp_rn(d1);
-                    const double l1 = b_div(t1, d1, r1);
-                    __syncwarp(mask);                               // every lane has read w before lane 0 overwrites it
-                    ucol[i] = u0; lcol[i] = l0; *pa0 = l0;
-                    if (tid == 0) *pa1 = d1;
-                    else { u1c[i] = t1; l1c[i] = l1; *pa1 = l1; }
-                }
-                __syncthreads();
-#pragma unroll
-                for (int h = 0; h < SN_EPT; h += SN_EPT / 2) {
-                    double u0v[SN_EPT / 2], l0v[SN_EPT / 2], u1v[SN_EPT / 2], l1v[SN_EPT / 2], av[SN_EPT / 2];
-#pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) {
-                        const int ij = eij[h + e];
-                        const bool on = h + e < ept && (ij >> 8) > k + 1;
-                        u0v[e] = on ? ucol[ij & 255] : 0.0; l0v[e] = on ? lcol[ij >> 8] : 0.0;
-                        u1v[e] = on ? u1c[ij & 255] : 0.0; l1v[e] = on ? l1c[ij >> 8] : 0.0;
-                        av[e] = on ? *ea[h + e] : 0.0;
-                    }
-#pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
-#pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
-#pragma unroll
-                    for (int e = 0; e < SN_EPT / 2; e++)
-                        if (h + e < ept && (eij[h + e] >> 8) > k + 1) *ea[h + e] = av[e];
-                }
-                __syncthreads();
-                k += 2;
-                continue;
-            }
             if (tid < N - k) {                                  // rows k+1 .. N (N = right-hand side)
                 const int i = k + 1 + tid;
                 double *pa = (i < N) ? L + pc + i : xs + f + k;
