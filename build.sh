@@ -17,6 +17,7 @@ done
 g++ -O2 -std=c++17 -fPIC -Iinclude -I$SRC -c $SRC/symbolic.cpp -o build/symbolic.o &
 g++ -O2 -std=c++17 -fPIC -Iinclude -I$SRC -c $SRC/ordering.cpp -o build/ordering.o &
 gcc -O2 -std=c99 -fPIC -Wall -Iinclude -c $SRC/qpdo_api.c -o build/qpdo_api.o &
+gcc -O2 -std=c99 -fPIC -Wall -Iinclude -c $SRC/qpdo_io.c -o build/qpdo_io.o &
 wait
 $NVCC $ARCH -shared -o "$OUT/libqpdo_b200.so" build/*.o -lcudart_static -lpthread -ldl -lrt -lm
 echo "built $OUT/libqpdo_b200.so"

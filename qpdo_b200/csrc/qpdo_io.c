@@ -1,0 +1,326 @@
+/* qpdo_io.c -- free-format QPS reader into the reference's QPDOData (include/qpdo_io.h).
+ *
+ * Host-only C.  The reference has no reader; the output is exactly what a C caller
+ * of qpdo_setup would build by hand (reference src/qpdo.c:49-110 deep-copies it): Q lower CSC with
+ * stype -1, A CSC with sorted row indices, l <= A x <= u with variable bounds as identity rows.
+ */
+#define _POSIX_C_SOURCE 200809L
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include "qpdo_io.h"
+
+/* ------------------------------------------------------------------ name table (open addressing) */
+typedef struct { char **name; long *slot; long count, cap, nslot; } names;
+
+static unsigned long hash_str(const char *s)
+{
+    unsigned long h = 1469598103934665603UL;
+    for (; *s; s++) { h ^= (unsigned char)*s; h *= 1099511628211UL; }
+    return h;
+}
+static int names_grow(names *t)
+{
+    long nslot = t->nslot ? 2 * t->nslot : 1024;
+    long *slot = malloc(sizeof(long) * nslot);
+    if (!slot) return -1;
+    for (long k = 0; k < nslot; k++) slot[k] = -1;
+    for (long k = 0; k < t->count; k++) {
+        unsigned long h = hash_str(t->name[k]) & (nslot - 1);
+        while (slot[h] >= 0) h = (h + 1) & (nslot - 1);
+        slot[h] = k;
+    }
+    free(t->slot);
+    t->slot = slot; t->nslot = nslot;
+    return 0;
+}
+static long names_find(const names *t, const char *s)
+{
+    if (!t->nslot) return -1;
+    unsigned long h = hash_str(s) & (t->nslot - 1);
+    while (t->slot[h] >= 0) {
+        if (strcmp(t->name[t->slot[h]], s) == 0) return t->slot[h];
+        h = (h + 1) & (t->nslot - 1);
+    }
+    return -1;
+}
+static long names_add(names *t, const char *s)        /* index of s, inserted when new; -2 on allocation failure */
+{
+    long k = names_find(t, s);
+    if (k >= 0) return k;
+    if (2 * (t->count + 1) > t->nslot && names_grow(t)) return -2;
+    if (t->count == t->cap) {
+        long cap = t->cap ? 2 * t->cap : 256;
+        char **nm = realloc(t->name, sizeof(char *) * cap);
+        if (!nm) return -2;
+        t->name = nm; t->cap = cap;
+    }
+    if (!(t->name[t->count] = strdup(s))) return -2;
+    unsigned long h = hash_str(s) & (t->nslot - 1);
+    while (t->slot[h] >= 0) h = (h + 1) & (t->nslot - 1);
+    t->slot[h] = t->count;
+    return t->count++;
+}
+static void names_free(names *t)
+{
+    for (long k = 0; k < t->count; k++) free(t->name[k]);
+    free(t->name); free(t->slot);
+    memset(t, 0, sizeof(*t));
+}
+
+/* ------------------------------------------------------------------ triplets -> CSC */
+typedef struct { long *r, *c; double *v; long count, cap; } triplets;
+
+static int trip_push(triplets *t, long r, long c, double v)
+{
+    if (t->count == t->cap) {
+        long cap = t->cap ? 2 * t->cap : 1024;
+        long *nr = realloc(t->r, sizeof(long) * cap);   if (!nr) return -1; t->r = nr;
+        long *nc = realloc(t->c, sizeof(long) * cap);   if (!nc) return -1; t->c = nc;
+        double *nv = realloc(t->v, sizeof(double) * cap); if (!nv) return -1; t->v = nv;
+        t->cap = cap;
+    }
+    t->r[t->count] = r; t->c[t->count] = c; t->v[t->count] = v; t->count++;
+    return 0;
+}
+static void trip_free(triplets *t) { free(t->r); free(t->c); free(t->v); memset(t, 0, sizeof(*t)); }
+
+/* CSC with sorted rows, duplicates summed (what cholmod_triplet_to_sparse does) */
+static cholmod_sparse *to_csc(const triplets *t, long nrow, long ncol, int stype)
+{
+    cholmod_sparse *S = calloc(1, sizeof(*S));
+    long *p = calloc((size_t)ncol + 1, sizeof(long));
+    long *ri = malloc(sizeof(long) * (size_t)(t->count ? t->count : 1));
+    double *x = malloc(sizeof(double) * (size_t)(t->count ? t->count : 1));
+    long *next = malloc(sizeof(long) * (size_t)(ncol ? ncol : 1));
+    if (!S || !p || !ri || !x || !next) { free(S); free(p); free(ri); free(x); free(next); return NULL; }
+    for (long k = 0; k < t->count; k++) p[t->c[k] + 1]++;
+    for (long j = 0; j < ncol; j++) { p[j + 1] += p[j]; next[j] = p[j]; }
+    for (long k = 0; k < t->count; k++) { long d = next[t->c[k]]++; ri[d] = t->r[k]; x[d] = t->v[k]; }
+    long out = 0;
+    for (long j = 0; j < ncol; j++) {
+        const long b = p[j], e = p[j + 1];
+        for (long a = b + 1; a < e; a++) {              /* insertion sort by row: columns are short */
+            long r = ri[a]; double v = x[a]; long q = a - 1;
+            while (q >= b && ri[q] > r) { ri[q + 1] = ri[q]; x[q + 1] = x[q]; q--; }
+            ri[q + 1] = r; x[q + 1] = v;
+        }
+        const long start = out;
+        for (long a = b; a < e; a++) {
+            if (out > start && ri[out - 1] == ri[a]) x[out - 1] += x[a];
+            else { ri[out] = ri[a]; x[out] = x[a]; out++; }
+        }
+        p[j] = start;
+    }
+    p[ncol] = out;
+    free(next);
+    S->nrow = (size_t)nrow; S->ncol = (size_t)ncol; S->nzmax = (size_t)(out ? out : 1);
+    S->p = p; S->i = ri; S->x = x; S->nz = NULL; S->z = NULL;
+    S->stype = stype; S->itype = 2; S->xtype = 1; S->dtype = 0; S->sorted = 1; S->packed = 1;
+    return S;
+}
+static void free_sparse(cholmod_sparse *S) { if (S) { free(S->p); free(S->i); free(S->x); free(S); } }
+
+void qpdo_free_data(QPDOData *d)
+{
+    if (!d) return;
+    free_sparse(d->Q); free_sparse(d->A);
+    free(d->q); free(d->l); free(d->u);
+    free(d);
+}
+
+/* ------------------------------------------------------------------ the reader */
+enum { S_NONE, S_ROWS, S_COLUMNS, S_RHS, S_RANGES, S_BOUNDS, S_QUADOBJ, S_QMATRIX, S_SKIP };
+
+static int split(char *line, char **tok, int maxtok)
+{
+    int n = 0;
+    char *save = NULL;
+    for (char *t = strtok_r(line, " \t\r\n", &save); t && n < maxtok; t = strtok_r(NULL, " \t\r\n", &save)) tok[n++] = t;
+    return n;
+}
+
+int qpdo_read_qps(const char *path, QPDOData **out, c_int *m_rows, c_int *err_line)
+{
+    if (out) *out = NULL;
+    if (err_line) *err_line = 0;
+    FILE *fp = path ? fopen(path, "r") : NULL;
+    if (!fp || !out) { if (fp) fclose(fp); return -1; }
+
+    names rows = {0}, cols = {0};
+    triplets At = {0}, Qt = {0};
+    char *rtype = NULL;           /* per row: 'N' 'E' 'L' 'G' */
+    long *rcon = NULL;            /* per row: constraint index or -1 */
+    double *rhs = NULL, *rng = NULL, *lo = NULL, *up = NULL;
+    char *has_rng = NULL;
+    long rcap = 0, ccap = 0, m0 = 0, objrow = -1, lineno = 0;
+    double cconst = 0.0;
+    int section = S_NONE, rc = 0;
+    char *line = NULL;
+    size_t lcap = 0;
+
+#define FAIL(code) do { rc = (code); goto done; } while (0)
+    while (getline(&line, &lcap, fp) >= 0) {
+        lineno++;
+        if (line[0] == '*' || line[0] == '\n' || line[0] == '\r' || line[0] == '\0') continue;
+        const int header = !(line[0] == ' ' || line[0] == '\t');
+        char *tok[8];
+        const int nt = split(line, tok, 8);
+        if (nt == 0) continue;
+        if (header) {
+            if (!strcmp(tok[0], "NAME")) section = S_NONE;
+            else if (!strcmp(tok[0], "ROWS")) section = S_ROWS;
+            else if (!strcmp(tok[0], "COLUMNS")) section = S_COLUMNS;
+            else if (!strcmp(tok[0], "RHS")) section = S_RHS;
+            else if (!strcmp(tok[0], "RANGES")) section = S_RANGES;
+            else if (!strcmp(tok[0], "BOUNDS")) section = S_BOUNDS;
+            else if (!strcmp(tok[0], "QUADOBJ")) section = S_QUADOBJ;
+            else if (!strcmp(tok[0], "QMATRIX")) section = S_QMATRIX;
+            else if (!strcmp(tok[0], "ENDATA")) break;
+            else section = S_SKIP;                    /* OBJSENSE, OBJSENSE MAX etc.: not supported, skipped */
+            continue;
+        }
+        switch (section) {
+        case S_ROWS: {
+            if (nt < 2) FAIL(-2);
+            const long before = rows.count, r = names_add(&rows, tok[1]);
+            if (r == -2) FAIL(-3);
+            if (r < before) FAIL(-2);                 /* duplicate row name */
+            if (rows.count > rcap) {
+                long cap = rcap ? 2 * rcap : 256;
+                char *a = realloc(rtype, (size_t)cap); if (!a) FAIL(-3); rtype = a;
+                long *b = realloc(rcon, sizeof(long) * cap); if (!b) FAIL(-3); rcon = b;
+                rcap = cap;
+            }
+            const char ty = tok[0][0];
+            if (ty != 'N' && ty != 'E' && ty != 'L' && ty != 'G') FAIL(-2);
+            rtype[r] = ty;
+            if (ty == 'N') { rcon[r] = -1; if (objrow < 0) objrow = r; }
+            else rcon[r] = m0++;
+            break;
+        }
+        case S_COLUMNS: {
+            if (nt >= 3 && !strcmp(tok[1], "'MARKER'")) break;
+            if (nt != 3 && nt != 5) FAIL(-2);
+            const long ncol_before = cols.count, j = names_add(&cols, tok[0]);
+            if (j == -2) FAIL(-3);
+            if (cols.count > ccap) {
+                long cap = ccap ? 2 * ccap : 256;
+                double *b = realloc(lo, sizeof(double) * cap); if (!b) FAIL(-3); lo = b;
+                double *c = realloc(up, sizeof(double) * cap); if (!c) FAIL(-3); up = c;
+                ccap = cap;
+            }
+            if (j >= ncol_before) { lo[j] = 0.0; up[j] = QPDO_INFTY; }       /* QPS default bounds [0, +inf) */
+            for (int k = 1; k + 1 < nt; k += 2) {
+                const long r = names_find(&rows, tok[k]);
+                if (r < 0) FAIL(-2);
+                const double v = strtod(tok[k + 1], NULL);
+                if (rcon[r] >= 0) { if (trip_push(&At, rcon[r], j, v)) FAIL(-3); }
+                else if (r == objrow) { if (trip_push(&Qt, -1, j, v)) FAIL(-3); }   /* linear cost, parked with row -1 */
+            }
+            break;
+        }
+        case S_RHS: case S_RANGES: {
+            if (!rhs) {
+                rhs = calloc((size_t)(m0 ? m0 : 1), sizeof(double)); rng = calloc((size_t)(m0 ? m0 : 1), sizeof(double));
+                has_rng = calloc((size_t)(m0 ? m0 : 1), 1);
+                if (!rhs || !rng || !has_rng) FAIL(-3);
+            }
+            const int first = (nt % 2) ? 1 : 0;       /* odd token count: the set name leads */
+            if (nt < 2) FAIL(-2);
+            for (int k = first; k + 1 < nt; k += 2) {
+                const long r = names_find(&rows, tok[k]);
+                if (r < 0) FAIL(-2);
+                const double v = strtod(tok[k + 1], NULL);
+                if (rcon[r] < 0) { if (section == S_RHS && r == objrow) cconst = -v; continue; }
+                if (section == S_RHS) rhs[rcon[r]] = v; else { rng[rcon[r]] = v; has_rng[rcon[r]] = 1; }
+            }
+            break;
+        }
+        case S_BOUNDS: {
+            /* type [set] column [value] */
+            const char *ty = tok[0];
+            const int noval = !strcmp(ty, "FR") || !strcmp(ty, "MI") || !strcmp(ty, "PL") || !strcmp(ty, "BV");
+            const char *cname; double v = 0.0;
+            if (noval) { if (nt == 2) cname = tok[1]; else if (nt >= 3) cname = tok[2]; else FAIL(-2); }
+            else { if (nt == 3) { cname = tok[1]; v = strtod(tok[2], NULL); } else if (nt >= 4) { cname = tok[2]; v = strtod(tok[3], NULL); } else FAIL(-2); }
+            const long j = names_find(&cols, cname);
+            if (j < 0) FAIL(-2);
+            if (!strcmp(ty, "UP") || !strcmp(ty, "UI")) { up[j] = v; if (v < 0.0 && lo[j] == 0.0) lo[j] = -QPDO_INFTY; }
+            else if (!strcmp(ty, "LO") || !strcmp(ty, "LI")) lo[j] = v;
+            else if (!strcmp(ty, "FX")) { lo[j] = v; up[j] = v; }
+            else if (!strcmp(ty, "FR")) { lo[j] = -QPDO_INFTY; up[j] = QPDO_INFTY; }
+            else if (!strcmp(ty, "MI")) lo[j] = -QPDO_INFTY;
+            else if (!strcmp(ty, "PL")) up[j] = QPDO_INFTY;
+            else if (!strcmp(ty, "BV")) { lo[j] = 0.0; up[j] = 1.0; }
+            else FAIL(-2);
+            break;
+        }
+        case S_QUADOBJ: case S_QMATRIX: {
+            if (nt != 3) FAIL(-2);
+            const long a = names_find(&cols, tok[0]), b = names_find(&cols, tok[1]);
+            if (a < 0 || b < 0) FAIL(-2);
+            const double v = strtod(tok[2], NULL);
+            if (section == S_QMATRIX && a < b) break;             /* both triangles listed: keep the lower one */
+            if (trip_push(&Qt, a > b ? a : b, a > b ? b : a, v)) FAIL(-3);
+            break;
+        }
+        default: break;
+        }
+    }
+    goto build;
+
+build: {
+        const long n = cols.count;
+        double *q = calloc((size_t)(n ? n : 1), sizeof(double));
+        if (!q) FAIL(-3);
+        /* split the parked cost entries (row -1) from the quadratic ones */
+        triplets Qq = {0};
+        for (long k = 0; k < Qt.count; k++) {
+            if (Qt.r[k] < 0) q[Qt.c[k]] += Qt.v[k];
+            else if (trip_push(&Qq, Qt.r[k], Qt.c[k], Qt.v[k])) { free(q); trip_free(&Qq); FAIL(-3); }
+        }
+        if (!rhs) { rhs = calloc((size_t)(m0 ? m0 : 1), sizeof(double)); rng = calloc((size_t)(m0 ? m0 : 1), sizeof(double)); has_rng = calloc((size_t)(m0 ? m0 : 1), 1); }
+        if (!rhs || !rng || !has_rng) { free(q); trip_free(&Qq); FAIL(-3); }
+        /* variable bounds -> identity rows */
+        long nb = 0;
+        for (long j = 0; j < n; j++) if (lo[j] > -QPDO_INFTY || up[j] < QPDO_INFTY) nb++;
+        const long m = m0 + nb;
+        double *l = malloc(sizeof(double) * (size_t)(m ? m : 1)), *u = malloc(sizeof(double) * (size_t)(m ? m : 1));
+        if (!l || !u) { free(q); free(l); free(u); trip_free(&Qq); FAIL(-3); }
+        for (long r = 0; r < rows.count; r++) {
+            const long i = rcon[r];
+            if (i < 0) continue;
+            const double b = rhs[i], R = rng[i];
+            switch (rtype[r]) {
+            case 'E': l[i] = b; u[i] = b; if (has_rng[i]) { if (R < 0) l[i] = b + R; else u[i] = b + R; } break;
+            case 'L': u[i] = b; l[i] = has_rng[i] ? b - fabs(R) : -QPDO_INFTY; break;
+            default:  l[i] = b; u[i] = has_rng[i] ? b + fabs(R) : QPDO_INFTY; break;       /* 'G' */
+            }
+        }
+        long i = m0;
+        int bad = 0;
+        for (long j = 0; j < n && !bad; j++)
+            if (lo[j] > -QPDO_INFTY || up[j] < QPDO_INFTY) {
+                bad = trip_push(&At, i, j, 1.0);
+                l[i] = lo[j] > -QPDO_INFTY ? lo[j] : -QPDO_INFTY; u[i] = up[j] < QPDO_INFTY ? up[j] : QPDO_INFTY; i++;
+            }
+        QPDOData *d = bad ? NULL : calloc(1, sizeof(*d));
+        if (!d) { free(q); free(l); free(u); trip_free(&Qq); FAIL(-3); }
+        d->n = (size_t)n; d->m = (size_t)m; d->q = q; d->c = cconst; d->l = l; d->u = u;
+        d->Q = to_csc(&Qq, n, n, -1);
+        d->A = to_csc(&At, m, n, 0);
+        trip_free(&Qq);
+        if (!d->Q || !d->A) { qpdo_free_data(d); FAIL(-3); }
+        *out = d;
+        if (m_rows) *m_rows = (c_int)m0;
+    }
+done:
+    if (rc == -2 && err_line) *err_line = (c_int)lineno;
+    free(line); fclose(fp);
+    names_free(&rows); names_free(&cols); trip_free(&At); trip_free(&Qt);
+    free(rtype); free(rcon); free(rhs); free(rng); free(has_rng); free(lo); free(up);
+    return rc;
+#undef FAIL
+}

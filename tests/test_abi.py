@@ -21,7 +21,7 @@ def declared_functions(header):
 @pytest.mark.parametrize("header", sorted(h for h in os.listdir(os.path.join(ROOT, "include")) if h.endswith(".h")))
 def test_library_exports_every_declared_symbol(cuda_lib, header):
     names = declared_functions(header)
-    assert len(names) >= 3, names
+    assert len(names) >= 2, names
     missing = [n for n in names if not hasattr(cuda_lib, n)]
     assert not missing, "declared in include/%s but not exported: %s" % (header, missing)
 
