@@ -504,6 +504,7 @@ __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *
         const int mycol = sn_col(base, lane, N);
         double v = 0.0;
         if (lane < nc) v = xs[f + lane]; else if (lane < N) v = xs[rows[lane - nc]];
+#ifdef B_BWD_UNROLLED
         double col[SN_NMAX];
 #pragma unroll
         for (int i = 1; i < SN_NMAX; i++) col[i] = (i < N && lane < nc && lane < i) ? L[mycol + i] : 0.0;
@@ -514,6 +515,17 @@ __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *
                 if (lane < i && lane < nc) v = fma(-col[i], xi, v);
             }
         }
+#else
+        // rolled: the L entry of step i is loaded while the broadcast of x_i is in flight (its address does not
+        // depend on the chain); 30 unrolled steps with the column in registers were 300 instructions and 60 registers
+        const int cend = lane < nc ? lane : -1;                  // lane updates while i > lane
+#pragma unroll 1
+        for (int i = N - 1; i >= 1; i--) {
+            const double lic = i > cend && cend >= 0 ? L[mycol + i] : 0.0;
+            const double xi = __shfl_sync(0xffffffffu, v, i);
+            if (i > cend && cend >= 0) v = fma(-lic, xi, v);
+        }
+#endif
         if (lane < nc) xs[f + lane] = v;
         __syncwarp();
     }
@@ -741,8 +753,13 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
 }
 
 // ------------------------------------------------------------------------------- one instance
-#define FOR_N(i) for (int i = threadIdx.x; i < n; i += BNT)
-#define FOR_M(i) for (int i = threadIdx.x; i < m; i += BNT)
+#ifdef B_UNROLL_VEC
+#define B_VEC_PRAGMA
+#else
+#define B_VEC_PRAGMA _Pragma("unroll 1")     // one or two trips per thread: unrolled copies only cost instruction fetch
+#endif
+#define FOR_N(i) B_VEC_PRAGMA for (int i = threadIdx.x; i < n; i += BNT)
+#define FOR_M(i) B_VEC_PRAGMA for (int i = threadIdx.x; i < m; i += BNT)
 
 #define B_TICK(slot) if (io.timing) { const long long now_ = clock64(); tacc[slot] += now_ - tlast; tlast = now_; }
 __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const BatchIO &io, const BVec &V, const int b)
