@@ -28,9 +28,13 @@
 #define B_MINCTAS 4              // resident CTAs per SM the register budget is sized for
 #endif
 #ifndef B_KUNROLL
-#define B_KUNROLL 4            // K assembly: product records in flight per thread
+#define B_KUNROLL 8            // K assembly: product records in flight per thread
 #endif
 constexpr int kKUnroll = B_KUNROLL;
+#ifndef B_SUNROLL
+#define B_SUNROLL 8            // gather SpMV: records in flight per thread
+#endif
+constexpr int kSUnroll = B_SUNROLL;
 #ifdef B_NOINLINE
 #define B_FN __noinline__
 #else
@@ -44,6 +48,11 @@ constexpr int kKUnroll = B_KUNROLL;
 #else
 #define B_LDS_IN(p) __ldcs(p)
 #define B_STS_OUT(p, v) __stcs((p), (v))
+#endif
+#ifdef B_UNROLL_LS
+#define B_LOOP1
+#else
+#define B_LOOP1 _Pragma("unroll 1")       // short-trip loops of the hot path stay rolled (instruction fetch)
 #endif
 #define B_INFTY 1e20
 #define LS_EXACT_MAX 128        // same threshold as linesearch.cu
@@ -177,7 +186,7 @@ __device__ B_SPMV_FN void b_ell_gather(int which, int nround, const int2 *round,
         const int2 rk = b_round(which, nround, round, r);
         const unsigned *T = rec + (size_t)rk.x * BNT + threadIdx.x;
         double s = 0.0;
-#pragma unroll 4
+#pragma unroll (kSUnroll)
         for (int k = 0; k < rk.y; k++) { const unsigned w = T[(size_t)k * BNT]; if (w != 0xffffffffu) s += val[w & 0xffffu] * x[w >> 16]; }
         const int i = r * BNT + threadIdx.x;
         if (i < nrows) y[i] = s;
@@ -197,7 +206,7 @@ __device__ __forceinline__ void b_spmv_Q(const BatchPlan &P, const double *Qv, c
         const int2 rk = b_round(2, P.ellQ.nround, P.ellQ.round, r);
         const unsigned *T = P.ellQ.rec + (size_t)rk.x * BNT + threadIdx.x;
         double s1 = 0.0, s2 = 0.0;
-#pragma unroll 4
+#pragma unroll (kSUnroll)
         for (int k = 0; k < rk.y; k++) {
             const unsigned w = T[(size_t)k * BNT];
             if (w != 0xffffffffu) {
@@ -573,10 +582,12 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
     __shared__ int kmin;
     __shared__ double wa[BNW], wb[BNW], tau_sh;
     double s[4] = {0, 0, 0, 0};
+    B_LOOP1
     for (int i = tid; i < m; i += BNT) {
         double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
         s[0] += V.dy[i] * tm; s[2] += V.y[i] * tm;
     }
+    B_LOOP1
     for (int i = tid; i < n; i += BNT) { s[1] += V.dx[i] * V.Qdx[i]; s[3] += V.dx[i] * V.df[i]; }
     const bool exact = (n <= LS_EXACT_MAX && M2 <= LS_EXACT_MAX);
     if (exact) {
@@ -634,6 +645,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
             } else { key[k] = kk; idx[k] = k < M2 ? k : 0; }
         } else if (compact && lane == 0) cw[r * BNW + wid] = 0;
     }
+    B_LOOP1
     for (int k = tid + RLMAX * BNT; k < P2; k += BNT) {    // only when !compact (2m > RLMAX * BNT / 2 ... large m)
         unsigned long long kk = ~0ull;
         if (k < M2) {
@@ -683,11 +695,13 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
                 if (kreg[r] != ~0ull) { key[mine + lpre[r]] = kreg[r]; idx[mine + lpre[r]] = tid + r * BNT; }
             }
         }
+        B_LOOP1
         for (int k = nLt + tid; k < P2e; k += BNT) { key[k] = ~0ull; idx[k] = 0; }
     }
     __syncthreads();
     for (int size = 2; size <= P2e; size <<= 1)
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            B_LOOP1
             for (int t = tid; t < (P2e >> 1); t += BNT) {
                 const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
                 const bool up = ((lo & size) == 0);
@@ -716,6 +730,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
     }
     const int chunk = (P2 + BNT - 1) / BNT, k0 = tid * chunk;
     double la = 0, lb = 0;
+    B_LOOP1
     for (int c = 0; c < chunk; c++) {
         const int k = k0 + c;
         if (k < nLt) { double da, db; b_ls_contrib(delta, alpha, idx[k], da, db); la += da; lb += db; }
@@ -728,9 +743,11 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
     if (lane == 31) { wa[wid] = pa; wb[wid] = pb; }
     __syncthreads();
     double oa = 0, ob = 0;
+    B_LOOP1
     for (int w = 0; w < wid; w++) { oa += wa[w]; ob += wb[w]; }
     double ra = a0 + (oa + pa - la), rb = b0 + (ob + pb - lb);
     double cand_a = 0, cand_b = 0; int cand_k = -1;
+    B_LOOP1
     for (int c = 0; c < chunk; c++) {
         const int k = k0 + c;
         if (k < nLt) {
