@@ -377,14 +377,10 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
     const unsigned Ls = b_saddr(L), xss = b_saddr(xs), uc = b_saddr(ucol);
     unsigned ea[SN_EPTS], pu[SN_EPTS], pl[SN_EPTS];       // N < 32: at most 495 owned entries, 4 per thread
 #pragma unroll
-    for (int e = 0; e < SN_EPTS; e++) {
-        ea[e] = Ls; pu[e] = uc; pl[e] = uc;                    // j = 0: never active
-        const int idx = tid + e * BNT;
-        if (e < ept && idx < ne) {
-            const int2 em = emap[idx];                          // i | j << 8, position in L (>= 0) or ~index into xs
-            ea[e] = em.y >= 0 ? Ls + 8u * (unsigned)em.y : xss + 8u * (unsigned)(~em.y);
-            pu[e] = uc + 8u * (unsigned)(em.x & 255); pl[e] = uc + 8u * (unsigned)(em.x >> 8);
-        }
+    for (int e = 0; e < SN_EPTS; e++) {                         // the table of a small front is padded to SN_EPTS * BNT entries (j = 0: never active)
+        const int2 em = emap[tid + e * BNT];                    // i | j << 8, position in L (>= 0) or ~index into xs
+        ea[e] = em.y >= 0 ? Ls + 8u * (unsigned)em.y : xss + 8u * (unsigned)(~em.y);
+        pu[e] = uc + 8u * (unsigned)(em.x & 255); pl[e] = uc + 8u * (unsigned)(em.x >> 8);
     }
     int k = 0;
     while (k < nc) {
@@ -528,8 +524,22 @@ __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *
         // rolled: the L entry of step i is loaded while the broadcast of x_i is in flight (its address does not
         // depend on the chain); 30 unrolled steps with the column in registers were 300 instructions and 60 registers
         const int cend = lane < nc ? lane : -1;                  // lane updates while i > lane
+#ifndef B_BWD_ONELOOP
+        {   // rows below the pivot block are final: their broadcasts read the initial values, not the chain
+            const double v0 = v;
+#pragma unroll 1
+            for (int i = N - 1; i >= nc; i--) {
+                const double lic = cend >= 0 ? L[mycol + i] : 0.0;
+                const double xi = __shfl_sync(0xffffffffu, v0, i);
+                if (cend >= 0) v = fma(-lic, xi, v);
+            }
+        }
+#pragma unroll 1
+        for (int i = nc - 1; i >= 1; i--) {
+#else
 #pragma unroll 1
         for (int i = N - 1; i >= 1; i--) {
+#endif
             const double lic = i > cend && cend >= 0 ? L[mycol + i] : 0.0;
             const double xi = __shfl_sync(0xffffffffu, v, i);
             if (i > cend && cend >= 0) v = fma(-lic, xi, v);
@@ -1301,9 +1311,14 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
                 else em.y = Upos[Uptr[sn] + (j - nc) * nr + (i - nc)];
                 Emap2.push_back(em);
             }
+            const int ne_real = (int)Emap2.size() - e0;
+            if (N < 32) {        // small fronts: padded to SN_EPTS * BNT entries (i = j = 0 never updates), so the kernel loads its four without bounds tests
+                int2 pad; pad.x = 0; pad.y = 0;
+                while ((int)Emap2.size() - e0 < SN_EPTS * BNT) Emap2.push_back(pad);
+            }
             int4 d0, d1;
             d0.x = f; d0.y = nc; d0.z = nr; d0.w = sn_base[sn];
-            d1.x = Sptr[sn]; d1.y = e0; d1.z = (int)Emap2.size() - e0; d1.w = 0;
+            d1.x = Sptr[sn]; d1.y = e0; d1.z = ne_real; d1.w = 0;
             sn_desc[2 * sn] = d0; sn_desc[2 * sn + 1] = d1;
         }
         // K entries -> packed positions
