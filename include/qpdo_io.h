@@ -28,8 +28,26 @@ extern "C" {
  * variable bounds, in column order. */
 int qpdo_read_qps(const char *path, QPDOData **out, c_int *m_rows, c_int *err_line);
 
-/* Frees a problem returned by qpdo_read_qps (NULL-safe). */
+/* Frees a problem returned by qpdo_read_qps / qpdo_read_mtx_problem (NULL-safe). */
 void qpdo_free_data(QPDOData *data);
+
+/* MatrixMarket (the format of CHOLMOD's reader, reference SuiteSparse/CHOLMOD/Check/cholmod_read.c;
+ * QPDO itself never calls it).  Reads "matrix coordinate|array real|integer|pattern
+ * general|symmetric|skew-symmetric" into CSC with sorted rows and summed duplicates: symmetric files
+ * give the lower triangle with stype = -1 (what qpdo_setup wants for Q), everything else stype = 0
+ * (skew-symmetric is expanded).  Same return codes as qpdo_read_qps. */
+int qpdo_read_mtx(const char *path, cholmod_sparse **out, c_int *err_line);
+void qpdo_free_sparse(cholmod_sparse *S);
+
+/* A vector stored as an n x 1 or 1 x n MatrixMarket matrix (array or coordinate); *out is malloc'ed. */
+int qpdo_read_mtx_vector(const char *path, c_float **out, c_int *len, c_int *err_line);
+
+/* A whole problem from MatrixMarket files.  A_path is required (m x n, general).  Q_path NULL = no
+ * quadratic term; a Q tagged general is reduced to its lower triangle.  q_path / l_path / u_path
+ * NULL = zeros / -QPDO_INFTY / +QPDO_INFTY; bounds beyond +-1e20 (or "inf") are clipped to +-QPDO_INFTY
+ * as qpdo.m:138-139 does.  -4 = the files' dimensions do not agree. */
+int qpdo_read_mtx_problem(const char *Q_path, const char *A_path, const char *q_path, const char *l_path,
+                          const char *u_path, QPDOData **out, c_int *err_line);
 
 #ifdef __cplusplus
 }

@@ -324,3 +324,195 @@ done:
     return rc;
 #undef FAIL
 }
+
+/* ------------------------------------------------------------------ MatrixMarket
+ * The format CHOLMOD's own reader takes (reference SuiteSparse/CHOLMOD/Check/cholmod_read.c, not used
+ * by QPDO itself).  Written from the format definition: banner "%%MatrixMarket matrix <coordinate|array>
+ * <real|integer|pattern> <general|symmetric|skew-symmetric>", '%' comments, a size line, then 1-based
+ * entries (coordinate) or column-major values (array). */
+enum { MM_GENERAL, MM_SYMMETRIC, MM_SKEW };
+
+static void lower_str(char *s) { for (; *s; s++) if (*s >= 'A' && *s <= 'Z') *s = (char)(*s - 'A' + 'a'); }
+
+/* Reads the banner and the size line.  coordinate: dims = nrow ncol nnz; array: dims = nrow ncol. */
+static int mm_header(FILE *fp, char **line, size_t *cap, long *lineno, int *is_array, int *is_pattern, int *sym, long dims[3])
+{
+    if (getline(line, cap, fp) < 0) return -2;
+    ++*lineno;
+    char *tok[8];
+    const int nt = split(*line, tok, 8);
+    if (nt < 5) return -2;
+    for (int k = 0; k < 5; k++) lower_str(tok[k]);
+    if (strcmp(tok[0], "%%matrixmarket") || strcmp(tok[1], "matrix")) return -2;
+    if (!strcmp(tok[2], "coordinate")) *is_array = 0; else if (!strcmp(tok[2], "array")) *is_array = 1; else return -2;
+    if (!strcmp(tok[3], "pattern")) *is_pattern = 1;
+    else if (!strcmp(tok[3], "real") || !strcmp(tok[3], "integer") || !strcmp(tok[3], "double")) *is_pattern = 0;
+    else return -2;                                                                  /* complex: not a QP */
+    if (!strcmp(tok[4], "general")) *sym = MM_GENERAL; else if (!strcmp(tok[4], "symmetric")) *sym = MM_SYMMETRIC;
+    else if (!strcmp(tok[4], "skew-symmetric")) *sym = MM_SKEW; else return -2;
+    if (*is_array && *is_pattern) return -2;
+    for (;;) {
+        if (getline(line, cap, fp) < 0) return -2;
+        ++*lineno;
+        const char *s = *line + strspn(*line, " \t\r\n");
+        if (*s == '%' || *s == '\0') continue;
+        const int want = *is_array ? 2 : 3;
+        char *end;
+        for (int k = 0; k < want; k++) {
+            dims[k] = strtol(s, &end, 10);
+            if (end == s || dims[k] < 0) return -2;
+            s = end;
+        }
+        if (s[strspn(s, " \t\r\n")] != '\0') return -2;
+        return 0;
+    }
+}
+
+int qpdo_read_mtx(const char *path, cholmod_sparse **out, c_int *err_line)
+{
+    if (out) *out = NULL;
+    if (err_line) *err_line = 0;
+    FILE *fp = path ? fopen(path, "r") : NULL;
+    if (!fp || !out) { if (fp) fclose(fp); return -1; }
+    char *line = NULL;
+    size_t cap = 0;
+    long lineno = 0, dims[3] = {0, 0, 0};
+    int is_array = 0, is_pattern = 0, sym = MM_GENERAL;
+    triplets T = {0};
+    int rc = mm_header(fp, &line, &cap, &lineno, &is_array, &is_pattern, &sym, dims);
+    const long nrow = dims[0], ncol = dims[1];
+    if (rc == 0 && sym != MM_GENERAL && nrow != ncol) rc = -2;
+    if (rc == 0 && !is_array) {
+        long seen = 0;
+        while (seen < dims[2]) {
+            if (getline(&line, &cap, fp) < 0) { rc = -2; break; }
+            lineno++;
+            const char *s = line + strspn(line, " \t\r\n");
+            if (*s == '%' || *s == '\0') continue;
+            char *end;
+            long i = strtol(s, &end, 10);  if (end == s) { rc = -2; break; }  s = end;
+            long j = strtol(s, &end, 10);  if (end == s) { rc = -2; break; }  s = end;
+            double v = 1.0;
+            if (!is_pattern) { v = strtod(s, &end); if (end == s) { rc = -2; break; } }
+            if (i < 1 || i > nrow || j < 1 || j > ncol) { rc = -2; break; }
+            i--; j--;
+            if (sym != MM_GENERAL && i < j) { long t = i; i = j; j = t; if (sym == MM_SKEW) v = -v; }   /* keep the lower triangle */
+            if (sym == MM_SKEW && i == j) { rc = -2; break; }
+            if (trip_push(&T, i, j, v)) { rc = -3; break; }
+            if (sym == MM_SKEW && trip_push(&T, j, i, -v)) { rc = -3; break; }
+            seen++;
+        }
+    } else if (rc == 0) {                                /* array: column-major; symmetric files hold the lower triangle */
+        for (long j = 0; j < ncol && rc == 0; j++)
+            for (long i = (sym == MM_GENERAL ? 0 : (sym == MM_SKEW ? j + 1 : j)); i < nrow && rc == 0; ) {
+                if (getline(&line, &cap, fp) < 0) { rc = -2; break; }
+                lineno++;
+                const char *s = line + strspn(line, " \t\r\n");
+                if (*s == '%' || *s == '\0') continue;
+                char *end;
+                for (;;) {                               /* several values on one line are accepted */
+                    const double v = strtod(s, &end);
+                    if (end == s) break;
+                    s = end;
+                    if (i >= nrow) { rc = -2; break; }
+                    if (v != 0.0 && trip_push(&T, i, j, v)) { rc = -3; break; }
+                    if (sym == MM_SKEW && v != 0.0 && trip_push(&T, j, i, -v)) { rc = -3; break; }
+                    i++;
+                }
+                if (rc == 0 && s[strspn(s, " \t\r\n")] != '\0') rc = -2;
+            }
+    }
+    if (rc == 0) {
+        *out = to_csc(&T, nrow, ncol, sym == MM_SYMMETRIC ? -1 : 0);
+        if (!*out) rc = -3;
+    }
+    if (rc == -2 && err_line) *err_line = (c_int)lineno;
+    trip_free(&T); free(line); fclose(fp);
+    return rc;
+}
+
+void qpdo_free_sparse(cholmod_sparse *S) { free_sparse(S); }
+
+int qpdo_read_mtx_vector(const char *path, c_float **out, c_int *len, c_int *err_line)
+{
+    if (out) *out = NULL;
+    if (len) *len = 0;
+    cholmod_sparse *S = NULL;
+    const int rc = out && len ? qpdo_read_mtx(path, &S, err_line) : -1;
+    if (rc) return rc;
+    if (S->ncol != 1 && S->nrow != 1) { free_sparse(S); return -2; }
+    const long n = (long)(S->ncol == 1 ? S->nrow : S->ncol);
+    double *v = calloc((size_t)(n ? n : 1), sizeof(double));
+    if (!v) { free_sparse(S); return -3; }
+    const long *p = S->p, *ri = S->i;
+    const double *x = S->x;
+    for (long j = 0; j < (long)S->ncol; j++)
+        for (long a = p[j]; a < p[j + 1]; a++) v[S->ncol == 1 ? ri[a] : j] = x[a];
+    free_sparse(S);
+    *out = v; *len = (c_int)n;
+    return 0;
+}
+
+/* Keeps the lower triangle of a general square matrix (a Q written without the symmetric tag). */
+static cholmod_sparse *lower_of(const cholmod_sparse *S)
+{
+    triplets T = {0};
+    const long *p = S->p, *ri = S->i;
+    const double *x = S->x;
+    for (long j = 0; j < (long)S->ncol; j++)
+        for (long a = p[j]; a < p[j + 1]; a++)
+            if (ri[a] >= j && trip_push(&T, ri[a], j, x[a])) { trip_free(&T); return NULL; }
+    cholmod_sparse *L = to_csc(&T, (long)S->nrow, (long)S->ncol, -1);
+    trip_free(&T);
+    return L;
+}
+
+int qpdo_read_mtx_problem(const char *Q_path, const char *A_path, const char *q_path, const char *l_path,
+                          const char *u_path, QPDOData **out, c_int *err_line)
+{
+    if (out) *out = NULL;
+    if (!out || !A_path) return -1;
+    QPDOData *d = calloc(1, sizeof(*d));
+    if (!d) return -3;
+    int rc = qpdo_read_mtx(A_path, &d->A, err_line);
+    if (rc == 0 && d->A->stype != 0) rc = -2;            /* A is a general matrix */
+    const long m = rc ? 0 : (long)d->A->nrow, n = rc ? 0 : (long)d->A->ncol;
+    if (rc == 0 && Q_path) {
+        rc = qpdo_read_mtx(Q_path, &d->Q, err_line);
+        if (rc == 0 && ((long)d->Q->nrow != n || (long)d->Q->ncol != n)) rc = -4;
+        if (rc == 0 && d->Q->stype == 0) {
+            cholmod_sparse *L = lower_of(d->Q);
+            free_sparse(d->Q); d->Q = L;
+            if (!L) rc = -3;
+        }
+    } else if (rc == 0) {                                /* no Q: an LP, the empty lower triangle */
+        triplets none = {0};
+        d->Q = to_csc(&none, n, n, -1);
+        if (!d->Q) rc = -3;
+    }
+    const char *vp[3] = { q_path, l_path, u_path };
+    double **dst[3] = { &d->q, &d->l, &d->u };
+    const double fill[3] = { 0.0, -QPDO_INFTY, QPDO_INFTY };
+    for (int k = 0; k < 3 && rc == 0; k++) {
+        const long want = k == 0 ? n : m;
+        if (vp[k]) {
+            c_int len = 0;
+            rc = qpdo_read_mtx_vector(vp[k], dst[k], &len, err_line);
+            if (rc == 0 && (long)len != want) rc = -4;
+        } else {
+            double *v = malloc(sizeof(double) * (size_t)(want ? want : 1));
+            if (!v) { rc = -3; break; }
+            for (long a = 0; a < want; a++) v[a] = fill[k];
+            *dst[k] = v;
+        }
+    }
+    if (rc == 0)
+        for (long i = 0; i < m; i++) {                   /* +-inf spelled as huge numbers or "inf" */
+            if (!(d->l[i] > -QPDO_INFTY)) d->l[i] = -QPDO_INFTY;
+            if (!(d->u[i] < QPDO_INFTY)) d->u[i] = QPDO_INFTY;
+        }
+    if (rc) { qpdo_free_data(d); return rc; }
+    d->n = (size_t)n; d->m = (size_t)m; d->c = 0.0;
+    *out = d;
+    return 0;
+}

@@ -89,3 +89,87 @@ def test_read_qps_cuda_matches_restatement(cuda_lib, oracle_mod, qps_file):
     s.delete()
     assert (r.status_val, r.iterations, r.oterations) == (o.status_val, o.iterations, o.oterations)
     assert rel_err(r.x, o.x) < 1e-8 and rel_err(r.y, o.y) < 1e-8
+
+
+# ---------------------------------------------------------------- MatrixMarket (qpdo_read_mtx*)
+def _write_mtx_problem(tmp_path, seed=3, n=12, m=9):
+    import scipy.io as sio
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    B = sp.random(n, n, 0.2, random_state=seed, format="csc")
+    Q = (B @ B.T + sp.identity(n)).tocsc()
+    A = sp.random(m, n, 0.4, random_state=seed + 1, format="csc")
+    q = rng.standard_normal(n)
+    l = -rng.random(m); u = rng.random(m)
+    l[0] = -np.inf; u[1] = 1e30                      # infinite bounds spelled two ways
+    sio.mmwrite(str(tmp_path / "Q.mtx"), Q, symmetry="symmetric")
+    sio.mmwrite(str(tmp_path / "Qg.mtx"), Q, symmetry="general")
+    sio.mmwrite(str(tmp_path / "A.mtx"), A)
+    sio.mmwrite(str(tmp_path / "q.mtx"), q.reshape(-1, 1))                    # array format
+    sio.mmwrite(str(tmp_path / "l.mtx"), sp.csc_matrix(np.where(np.isinf(l), -1e21, l).reshape(-1, 1)))   # coordinate n x 1
+    (tmp_path / "u.mtx").write_text("%%MatrixMarket matrix array real general\n% upper bounds\n1 {}\n".format(m)
+                                    + "\n".join("inf" if v > 1e20 else repr(float(v)) for v in u) + "\n")
+    return Q, A, q, l, u
+
+
+def test_read_mtx_problem_arrays(cuda_lib, tmp_path):
+    import scipy.sparse as sp
+    Q, A, q, l, u = _write_mtx_problem(tmp_path)
+    S, stype = qio.read_mtx(tmp_path / "Q.mtx", cuda_lib)
+    assert stype == -1 and abs(S - sp.tril(Q)).max() < 1e-15 and sp.triu(S, 1).nnz == 0
+    S, stype = qio.read_mtx(tmp_path / "A.mtx", cuda_lib)
+    assert stype == 0 and S.has_sorted_indices and abs(S - A).max() < 1e-15
+    for qfile in ("Q.mtx", "Qg.mtx"):
+        d = qio.read_mtx_problem(tmp_path / "A.mtx", tmp_path / qfile, tmp_path / "q.mtx", tmp_path / "l.mtx", tmp_path / "u.mtx", cuda_lib)
+        assert abs(d["Q"] - Q).max() < 1e-15 and abs(d["A"] - A).max() < 1e-15
+        assert np.allclose(d["q"], q, rtol=0, atol=1e-15)
+        assert d["l"][0] == -INF and d["u"][1] == INF
+        assert np.allclose(d["l"][1:], l[1:], rtol=0, atol=1e-15) and np.allclose(np.delete(d["u"], 1), np.delete(u, 1), rtol=0, atol=1e-15)
+    d = qio.read_mtx_problem(tmp_path / "A.mtx", lib=cuda_lib)          # defaults: LP with free rows
+    assert d["Q"].nnz == 0 and not d["q"].any() and np.all(d["l"] == -INF) and np.all(d["u"] == INF)
+
+
+def test_read_mtx_pattern_skew_and_errors(cuda_lib, tmp_path):
+    (tmp_path / "p.mtx").write_text("%%MatrixMarket matrix coordinate pattern symmetric\n3 3 3\n1 1\n3 1\n2 3\n")
+    S, stype = qio.read_mtx(tmp_path / "p.mtx", cuda_lib)
+    assert stype == -1 and np.array_equal(S.toarray(), [[1, 0, 0], [0, 0, 0], [1, 1, 0]])
+    (tmp_path / "k.mtx").write_text("%%MatrixMarket matrix coordinate real skew-symmetric\n2 2 1\n2 1 3.5\n")
+    S, stype = qio.read_mtx(tmp_path / "k.mtx", cuda_lib)
+    assert stype == 0 and np.array_equal(S.toarray(), [[0, -3.5], [3.5, 0]])
+    (tmp_path / "d.mtx").write_text("%%MatrixMarket matrix coordinate real general\n2 2 3\n1 1 1.0\n1 1 2.0\n2 1 -1\n")
+    S, _ = qio.read_mtx(tmp_path / "d.mtx", cuda_lib)                   # duplicates are summed
+    assert np.array_equal(S.toarray(), [[3, 0], [-1, 0]])
+    with pytest.raises(OSError):
+        qio.read_mtx(tmp_path / "missing.mtx", cuda_lib)
+    (tmp_path / "bad.mtx").write_text("%%MatrixMarket matrix coordinate real general\n2 2 2\n1 1 1.0\n3 1 2.0\n")
+    with pytest.raises(ValueError, match="line 4"):
+        qio.read_mtx(tmp_path / "bad.mtx", cuda_lib)
+    (tmp_path / "cplx.mtx").write_text("%%MatrixMarket matrix coordinate complex general\n1 1 1\n1 1 1.0 0.0\n")
+    with pytest.raises(ValueError, match="line 1"):
+        qio.read_mtx(tmp_path / "cplx.mtx", cuda_lib)
+    Q, A, q, l, u = _write_mtx_problem(tmp_path)
+    with pytest.raises(ValueError, match="dimensions"):
+        qio.read_mtx_problem(tmp_path / "A.mtx", tmp_path / "Q.mtx", tmp_path / "l.mtx", lib=cuda_lib)   # q of length m
+
+
+def test_read_mtx_problem_solves_on_the_oracle(cuda_lib, oracle_mod, tmp_path):
+    _write_mtx_problem(tmp_path)
+    d = qio.read_mtx_problem(tmp_path / "A.mtx", tmp_path / "Q.mtx", tmp_path / "q.mtx", tmp_path / "l.mtx", tmp_path / "u.mtx", cuda_lib)
+    o = oracle_mod.solve(d, trace=False)
+    assert o.status_val == 1
+    x = np.asarray(o.x)
+    assert np.abs(d["Q"] @ x + d["q"] + d["A"].T @ np.asarray(o.y)).max() < 1e-5
+
+
+@pytest.mark.gpu
+def test_read_mtx_problem_cuda_matches_restatement(cuda_lib, oracle_mod, tmp_path):
+    from qpdo_b200 import QPDO
+    _write_mtx_problem(tmp_path)
+    d = qio.read_mtx_problem(tmp_path / "A.mtx", tmp_path / "Q.mtx", tmp_path / "q.mtx", tmp_path / "l.mtx", tmp_path / "u.mtx", cuda_lib)
+    o = oracle_mod.solve(d, trace=False)
+    s = QPDO()
+    s.setup(d["Q"], d["q"], d["A"], d["l"], d["u"], dict(verbose=0))
+    r = s.solve()
+    s.delete()
+    assert (r.status_val, r.iterations, r.oterations) == (o.status_val, o.iterations, o.oterations)
+    assert rel_err(r.x, o.x) < 1e-8 and rel_err(r.y, o.y) < 1e-8

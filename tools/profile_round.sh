@@ -19,9 +19,12 @@ step "bench c5 (default)"
 python bench.py > $O/${TAG}_bench_c5.json 2> $O/${TAG}_bench_c5.err; echo "rc=$?"
 step "bench c5 --impl reference"
 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_c5_reference.json 2> $O/${TAG}_bench_c5_reference.err; echo "rc=$?"
+C3RC=1
+if [ "$SKIP_C3" != 1 ]; then
 step "bench c3"
 python bench.py --workload c3 --steps 2 --warmup 1 > $O/${TAG}_bench_c3.json 2> $O/${TAG}_bench_c3.err; C3RC=$?; echo "rc=$C3RC"
-if [ "$SKIP_C3_REF" != 1 ]; then
+fi
+if [ "$SKIP_C3_REF" != 1 ] && [ "$SKIP_C3" != 1 ]; then
 step "bench c3 --impl reference"
 python bench.py --workload c3 --impl reference --steps 1 --warmup 0 > $O/${TAG}_bench_c3_reference.json 2> $O/${TAG}_bench_c3_reference.err; echo "rc=$?"
 fi
