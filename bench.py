@@ -235,7 +235,7 @@ from qpdo_b200 import batch as qbatch      # ctypes mirror of include/qpdo_batch
 import ctypes as C
 
 C5_BATCH = 65536
-TRAFFIC_PER_QP_NCU = 11256          # measured DRAM bytes per QP (26.62 MB read + 0.04 MB written back inside the launch, 2,368 QPs; results reach DRAM after the launch)
+TRAFFIC_PER_QP_NCU = 11180          # measured DRAM bytes per QP (26.47 MB read + 0.001 MB written back inside the launch, 2,368 QPs; results reach DRAM after the launch)
 
 
 def algorithmic_bytes_per_qp(n, m, nnzQ, nnzA):
