@@ -121,6 +121,13 @@ int  qpdo_dev_test_factor_solve(qpdo_dev *d, const double *omega, double sigma, 
                                 double *x, float *factor_ms, float *solve_ms);
 /* y = A x, y = A' x, y = Q x on the device-resident (scaled) matrices; which: 0 A, 1 A', 2 Q */
 int  qpdo_dev_test_spmv(qpdo_dev *d, int which, const double *x, double *y);
+/* exact_linesearch (linesearch.c:8-158) alone on host vectors of the workspace's sizes (dx, Qdx, df: n;
+ * the rest: m): test hook for the breakpoint build / sort / sweep kernels; overwrites the iterate
+ * vectors of the workspace, so call it on a workspace that is not solved afterwards */
+int  qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const double *Qdx, const double *df,
+                              const double *dy, const double *y, const double *mu, const double *sqrt_mu,
+                              const double *Adx, const double *w, const double *l, const double *u,
+                              double *tau);
 
 #ifdef __cplusplus
 }

@@ -777,6 +777,23 @@ extern "C" int qpdo_dev_test_spmv(qpdo_dev *d, int which, const double *x, doubl
     return 0;
 }
 
+extern "C" int qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const double *Qdx, const double *df, const double *dy,
+                                        const double *y, const double *mu, const double *sqrt_mu, const double *Adx,
+                                        const double *w, const double *l, const double *u, double *tau)
+{
+    struct { double *dst; const double *src; int len; } up[] = {
+        {d->dx, dx, d->n}, {d->Qdx, Qdx, d->n}, {d->df, df, d->n}, {d->dy, dy, d->m}, {d->y, y, d->m}, {d->mu, mu, d->m},
+        {d->sqrt_mu, sqrt_mu, d->m}, {d->Adx, Adx, d->m}, {d->w, w, d->m}, {d->l, l, d->m}, {d->u, u, d->m}};
+    for (auto &v : up)
+        if (v.len > 0) CUDA_OK(cudaMemcpyAsync(v.dst, v.src, sizeof(double) * v.len, cudaMemcpyHostToDevice, d->st));
+    if (linesearch_run(d)) return -1;
+    qpdo_dev_scalars h;
+    CUDA_OK(cudaMemcpyAsync(&h, d->sc, sizeof(h), cudaMemcpyDeviceToHost, d->st));
+    CUDA_OK(cudaStreamSynchronize(d->st));
+    *tau = h.tau;
+    return 0;
+}
+
 extern "C" int qpdo_dev_test_factor_solve(qpdo_dev *d, const double *omega, double sigma, const double *b, double *x,
                                           float *factor_ms, float *solve_ms)
 {

@@ -260,3 +260,42 @@ def test_edge_cases_no_constraints_and_scalar_problem(oracle_mod):
         assert (r.status_val, r.iterations, r.oterations) == e
         assert rel_err(o.x, r.x) <= TOL and (o.y.size == 0 or rel_err(o.y, r.y) <= TOL)
         assert abs(r.objective - o.objective) <= TOL * max(1.0, abs(o.objective))
+
+
+@pytest.mark.parametrize("n,m,case", [(20, 30, "root"), (40, 1000, "root"), (40, 1500, "root"), (30, 40000, "root"),
+                                      (30, 40000, "ties"), (30, 6000, "no_breakpoint"), (30, 6000, "inf_bounds")])
+def test_linesearch_kernels_against_restatement(cuda_lib, oracle_mod, n, m, case):
+    """exact_linesearch alone (linesearch.c:8-158): the one-CTA bitonic path (2m <= 2048) and the breakpoint build ->
+    8-pass radix sort -> block sweep path against the restatement's qsort + sequential sweep on the same vectors.
+    Tolerance 1e-10 relative: the sweep's prefix sums are blocked on the GPU, sequential in the reference."""
+    import qpdo_b200
+    L = oracle_mod.lib()
+    p = problems.random_qp(n, m, min(1.0, 4.0 / n), seed=5)
+    s = qpdo_b200.QPDO()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0, scaling=0))
+    rng = np.random.default_rng(n + m)
+    dx, dy, Adx = rng.standard_normal(n), rng.standard_normal(m), rng.standard_normal(m)
+    Qdx = dx * rng.uniform(0.5, 2.0, n)
+    mu = rng.uniform(0.01, 10, m); sqrt_mu = 1 / np.sqrt(mu)
+    l = -rng.random(m); u = rng.random(m)
+    w = l + (u - l) * rng.random(m)
+    df = -10.0 * dx; y = -dy
+    if case == "ties":                               # many equal breakpoints: the sort order of equal keys must not matter
+        mu[:] = 1.0; sqrt_mu[:] = 1.0
+        dy[:] = 0.0; y[:] = 0.0
+        Adx = rng.choice([-1.0, 1.0, 2.0], m); l[:] = -1.0; u[:] = 1.0; w = rng.choice([-0.5, 0.0, 0.5], m)
+    elif case == "no_breakpoint":                    # the root lies before the first breakpoint: tau = -beta / eta
+        df = -1e-6 * dx
+        y = -1e-6 * dy
+    elif case == "inf_bounds":
+        l[::2] = -1e20; u[1::3] = 1e20
+    args = [np.ascontiguousarray(a, dtype=np.float64) for a in (dx, Qdx, df, dy, y, mu, sqrt_mu, Adx, w, l, u)]
+    ptrs = [a.ctypes.data_as(_pd) for a in args]
+    tau_ref = L.qpdo_oracle_linesearch(n, m, *ptrs)
+    tau = C.c_double(-1.0)
+    cuda_lib.qpdo_dev_test_linesearch.argtypes = [C.c_void_p] + [_pd] * 11 + [C.POINTER(C.c_double)]
+    cuda_lib.qpdo_dev_test_linesearch.restype = C.c_int
+    assert cuda_lib.qpdo_dev_test_linesearch(s.device, *ptrs, C.byref(tau)) == 0
+    s.delete()
+    assert tau_ref > 0
+    assert abs(tau.value - tau_ref) <= 1e-10 * abs(tau_ref), (tau.value, tau_ref)
