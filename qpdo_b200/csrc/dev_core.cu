@@ -351,6 +351,43 @@ extern "C" int qpdo_dev_get_scaling(qpdo_dev *d, double *D, double *Dinv, double
     return 0;
 }
 
+// qpdo_update_settings with more scaling sweeps (qpdo.c:496-512): the extra sweeps run on the already scaled data
+// exactly as a fresh scale_data would (D, E restart from 1; Q, q, l, u are scaled by the increment; the cost scale is
+// recomputed with the CURRENT Qx, as the reference does), then the total D, E, c are the products with the saved ones.
+// The iterates are left as they are, like in the reference: callers warm-start afterwards.
+extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
+{
+    if (extra_iters <= 0) return 0;
+    if (d->scaling_iters <= 0) {      // the reference dereferences work->scaling == NULL here (qpdo.c:498): an error instead
+        qpdo_set_error("qpdo_update_settings: scaling cannot be switched on after a setup with scaling = 0");
+        return -3;
+    }
+    const int n = d->n, m = d->m, T = 128;
+    double *save = nullptr;
+    CUDA_OK(cudaMalloc(&save, sizeof(double) * ((size_t)n + m + 1)));
+    double *saveD = save, *saveE = save + n;
+    const double c_old = d->c;
+    int rc = -1;
+    do {
+        if (cudaMemcpyAsync(saveD, d->D, sizeof(double) * n, cudaMemcpyDeviceToDevice, d->st) != cudaSuccess) break;
+        if (m && cudaMemcpyAsync(saveE, d->E, sizeof(double) * m, cudaMemcpyDeviceToDevice, d->st) != cudaSuccess) break;
+        if (run_scaling(d, extra_iters)) break;
+        k_ew_prod<<<cdiv(n, T), T, 0, d->st>>>(d->D, saveD, d->D, n);
+        if (m) k_ew_prod<<<cdiv(m, T), T, 0, d->st>>>(d->E, saveE, d->E, m);
+        d->c = d->c * c_old;
+        k_recip<<<cdiv(n, T), T, 0, d->st>>>(d->D, d->Dinv, n);
+        if (m) k_recip<<<cdiv(m, T), T, 0, d->st>>>(d->E, d->Einv, m);
+        d->cinv = 1.0 / d->c;
+        d->scaling_iters += extra_iters;
+        if (refresh_matrix_copies(d)) break;       // norm_q is left as it was, like in the reference (nothing reads it)
+        rc = 0;
+    } while (0);
+    cudaStreamSynchronize(d->st);
+    cudaFree(save);
+    if (rc) qpdo_set_error("qpdo_dev_rescale failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return rc;
+}
+
 extern "C" int qpdo_dev_get_symbolic_info(qpdo_dev *d, qpdo_dev_symbolic_info *o)
 {
     const qpdo_symbolic *S = d->F.S;

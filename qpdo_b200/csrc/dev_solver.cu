@@ -734,15 +734,6 @@ extern "C" int qpdo_dev_update_q(qpdo_dev *d, const double *q, int proximal, dou
     return 0;
 }
 
-extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
-{
-    (void)extra_iters;
-    qpdo_set_error("qpdo_update_settings: increasing the number of scaling sweeps after setup is not implemented yet "
-                   "(SURVEY 8(f)-1); call qpdo_setup again");
-    (void)d;
-    return -3;
-}
-
 extern "C" long qpdo_dev_get_vector(qpdo_dev *d, const char *name, double *out, long cap)
 {
     struct { const char *nm; const double *p; int len; } tab[] = {

@@ -474,6 +474,13 @@ void qpdo_update_settings(QPDOWorkspace *work, const QPDOSettings *settings)
             update_status(work->info, QPDO_ERROR);
             return;
         }
+        /* host mirror of the total scaling (qpdo.c:503-511) */
+        if (qpdo_dev_get_scaling(DEV(work), work->scaling->D, work->scaling->Dinv, work->scaling->E, work->scaling->Einv,
+                                 &work->scaling->c, &work->scaling->cinv, NULL)) {
+            eprint("CUDA layer: %s", qpdo_dev_last_error());
+            update_status(work->info, QPDO_ERROR);
+            return;
+        }
     }
     free(work->settings);
     work->settings = copy_settings(settings);

@@ -299,3 +299,34 @@ def test_linesearch_kernels_against_restatement(cuda_lib, oracle_mod, n, m, case
     s.delete()
     assert tau_ref > 0
     assert abs(tau.value - tau_ref) <= 1e-10 * abs(tau_ref), (tau.value, tau_ref)
+
+
+def test_update_settings_more_scaling_sweeps_against_reference_golden():
+    """qpdo_update_settings with more Ruiz sweeps (qpdo.c:496-512): incremental scaling on the device, total D, E, c,
+    then a warm-started solve; golden from the unmodified reference (tests/golden/make_golden_rescale.py)."""
+    import os
+    import qpdo_b200
+    sys_path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(sys_path, "rescale_seq.npz"))
+    p = problems.random_qp(120, 80, 0.05, seed=11)
+    s = qpdo_b200.QPDO()
+    s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0, scaling=2))
+    a = s.solve()
+    assert [a.status_val, a.iterations, a.oterations] == list(g["info1"])
+    assert rel_err(a.x, g["x1"]) <= TOL and rel_err(a.y, g["y1"]) <= TOL
+    s.update_settings(dict(verbose=0, scaling=10))
+    w = s.work
+    assert w.info.contents.status_val != -99          # QPDO_ERROR
+    D = np.ctypeslib.as_array(w.scaling.contents.D, shape=(s.n,))
+    E = np.ctypeslib.as_array(w.scaling.contents.E, shape=(s.m,))
+    assert rel_err(D, g["D"]) <= 1e-13 and rel_err(E, g["E"]) <= 1e-13 and abs(w.scaling.contents.c - float(g["c"])) <= 1e-13 * float(g["c"])
+    s.warm_start(a.x, a.y)
+    b = s.solve()
+    assert [b.status_val, b.iterations, b.oterations] == list(g["info2"])
+    assert np.array_equal(np.asarray(b.active_set), g["active2"])
+    assert rel_err(b.x, g["x2"]) <= TOL and rel_err(b.y, g["y2"]) <= TOL
+    assert abs(b.objective - float(g["obj2"])) <= TOL * abs(float(g["obj2"]))
+    # decreasing is refused with QPDO_ERROR and leaves the settings alone (qpdo.c:490-495)
+    s.update_settings(dict(verbose=0, scaling=3))
+    assert s.work.info.contents.status_val == -99 and s.work.settings.contents.scaling == 10
+    s.delete()
