@@ -353,7 +353,8 @@ extern "C" int qpdo_dev_get_scaling(qpdo_dev *d, double *D, double *Dinv, double
 
 // qpdo_update_settings with more scaling sweeps (qpdo.c:496-512): the extra sweeps run on the already scaled data
 // exactly as a fresh scale_data would (D, E restart from 1; Q, q, l, u are scaled by the increment; the cost scale is
-// recomputed with the CURRENT Qx, as the reference does), then the total D, E, c are the products with the saved ones.
+// recomputed with the CURRENT Qx, as the reference does), then the total D, E, c are the products with the saved ones
+// (see the note on D below).
 // The iterates are left as they are, like in the reference: callers warm-start afterwards.
 extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
 {
@@ -372,7 +373,12 @@ extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
         if (cudaMemcpyAsync(saveD, d->D, sizeof(double) * n, cudaMemcpyDeviceToDevice, d->st) != cudaSuccess) break;
         if (m && cudaMemcpyAsync(saveE, d->E, sizeof(double) * m, cudaMemcpyDeviceToDevice, d->st) != cudaSuccess) break;
         if (run_scaling(d, extra_iters)) break;
-        k_ew_prod<<<cdiv(n, T), T, 0, d->st>>>(d->D, saveD, d->D, n);
+        // The reference multiplies by work->temp_n, which its own scale_data has meanwhile overwritten with Qx + q
+        // (scaling.c:68 after qpdo.c:498): its total D is D_increment o (Qx + q), not D_increment o D_old, and every
+        // later un-scaling of x is off.  Default here: the documented intent (product with the saved D).
+        // QPDO_B200_COMPAT_RESCALE=1 reproduces the reference bit for bit (d->tmp_n still holds Qx + q).
+        const char *compat = getenv("QPDO_B200_COMPAT_RESCALE");
+        k_ew_prod<<<cdiv(n, T), T, 0, d->st>>>(d->D, (compat && compat[0] == '1') ? d->tmp_n : saveD, d->D, n);
         if (m) k_ew_prod<<<cdiv(m, T), T, 0, d->st>>>(d->E, saveE, d->E, m);
         d->c = d->c * c_old;
         k_recip<<<cdiv(n, T), T, 0, d->st>>>(d->D, d->Dinv, n);
