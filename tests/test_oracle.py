@@ -9,22 +9,25 @@ from qpdo_b200 import problems
 CASES, checksum = golden_cases()
 TOL = 1e-8          # north_star: x, y, objective within 1e-8 relative
 
-# the reference's dual-infeasibility test sits on a knife edge for this fixture (sigma == eps_dual_inf,
-# decided by 1e-12 of rank-1 downdate noise inside CHOLMOD, see DESIGN.md "known deviations"):
-# status matches, detection comes one outer iteration earlier
-KNIFE_EDGE = {"dual_infeasible"}
+# The reference's dual-infeasibility test sits on a knife edge for this fixture: at outer iteration 4 it
+# reads sigma*tau <= eps_dual_inf with sigma == eps_dual_inf, i.e. tau <= 1, and the reference's tau is
+# 1 + 1.0e-12 -- the residue of ONE rank-1 downdate (10.001 - 10) at pass 1 (trace and arithmetic:
+# profiles/r2_knife_edge.json, made by tools/knife_edge.py).  A refactoring solver has tau = 1 - 1 ulp,
+# passes that test and stops exactly one outer iteration (two loop passes) earlier: asserted exactly.
+KNIFE_EDGE = {"dual_infeasible": (-2, -1)}      # (iterations, oterations) relative to the reference
 SLOW = {"c1"}
-# relaxing CONT's equality rows into 0.15-wide ranges makes a degenerate problem whose several-hundred-
-# iteration solve amplifies rounding differences of ANY two factorizations: status + objective only
-CHAOTIC_SEQ = {"cont20", "cont40"}
+# CONT-40 with its equality rows relaxed into 0.15-wide ranges is a degenerate ~440-pass solve on which the
+# UNMODIFIED reference gives 10 different iteration totals (408..445) in 10 runs that differ by one ulp in
+# one entry of q (profiles/r2_knife_edge.json): status + objective only.  CONT-20 is stable and exact.
+CHAOTIC_SEQ = {"cont40"}
 
 
 TOL_SEQ = 1e-6      # long parametric re-solves of (near-)degenerate problems: x is only determined to eps_abs
 
 
-def check(tag, g, r, prefix, exact_iters=True, TOL=TOL):
+def check(tag, g, r, prefix, knife=None, TOL=TOL):
     assert r.status_val == int(g[prefix + "status_val"]), tag
-    if exact_iters:
+    if knife is None:
         assert r.iterations == int(g[prefix + "iterations"]), tag
         assert r.oterations == int(g[prefix + "oterations"]), tag
         assert np.array_equal(r.active_set, g[prefix + "active_set"]), tag
@@ -35,7 +38,9 @@ def check(tag, g, r, prefix, exact_iters=True, TOL=TOL):
         if r.status_val == -3:
             assert rel_err(g[prefix + "prim_inf_cert"], r.prim_inf_cert) <= 1e-6, tag
     else:
-        assert r.iterations <= int(g[prefix + "iterations"]), tag
+        assert r.iterations == int(g[prefix + "iterations"]) + knife[0], tag
+        assert r.oterations == int(g[prefix + "oterations"]) + knife[1], tag
+        assert np.array_equal(r.active_set, g[prefix + "active_set"]), tag
         if r.status_val == -4:
             a = g[prefix + "dual_inf_cert"]; b = r.dual_inf_cert
             assert rel_err(a / np.abs(a).max(), b / np.abs(b).max()) <= 1e-6, tag
@@ -48,7 +53,7 @@ def test_restatement_matches_reference_golden(oracle_mod, name):
     g = load_golden(name)
     assert checksum(p) == str(g["checksum"]), "problem generator drifted from the golden fixture"
     r = oracle_mod.solve(p, st)
-    check(name + "/cold", g, r, "cold_", exact_iters=name not in KNIFE_EDGE)
+    check(name + "/cold", g, r, "cold_", knife=KNIFE_EDGE.get(name))
     if "warm_status_val" in g.files:
         rw = oracle_mod.solve(p, st, x0=g["cold_x"] * (1 + 1e-3), y0=g["cold_y"] * (1 - 1e-3))
         check(name + "/warm", g, rw, "warm_")
