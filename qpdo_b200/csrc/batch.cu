@@ -326,9 +326,9 @@ __device__ __forceinline__ void b_backward(const BatchPlan &P, const double *K, 
 #define SN_NMAX 31              // b_backward_sn: front order limit (one lane per front row)
 __device__ __forceinline__ int sn_col(int base, int jj, int N) { return base + jj * N - ((jj * (jj - 1)) >> 1) - jj; }   // + front row i
 #define SN_EPT 8
-#define SN_DESC_MAX 64          // supernode descriptors cached in shared memory (else read from global)
+#define SN_DESC_MAX 16          // supernode descriptors cached in shared memory (else read from global)
 __shared__ int4 s_desc[2 * SN_DESC_MAX];   // {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
-#define SN_ROWS_MAX 512         // rows below the pivot blocks (all supernodes) cached in shared memory
+#define SN_ROWS_MAX 128         // rows below the pivot blocks (all supernodes) cached in shared memory
 __shared__ int s_rows[SN_ROWS_MAX];
 __device__ __forceinline__ int4 sn_desc(const BatchPlan &P, int s, int which) { return P.nsuper <= SN_DESC_MAX ? s_desc[2 * s + which] : P.sn_desc[2 * s + which]; }
 // ---- fronts of order N < 32 (rows k+1 .. N of a column pair sit in one warp).  The owners keep three 32-bit
@@ -348,32 +348,101 @@ __device__ __forceinline__ void b_sts_if(unsigned a, double v, bool p)
 {
     asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.shared.f64 [%0], %1; }" :: "r"(a), "d"(v), "r"((unsigned)p) : "memory");
 }
-// both rank-1 updates of a pivot pair on the owned entries of slots E0 .. SN_EPTS-1 (all loads, then the fma's, then
-// the predicated stores)
-template <int E0> __device__ __forceinline__ void b_pair_update(const unsigned (&ea)[SN_EPTS], const unsigned (&pu)[SN_EPTS],
-                                                                 const unsigned (&pl)[SN_EPTS], unsigned thr)
+// ---- panel step: up to SN_PW pivots per barrier pair.  Warp 0 holds one front row per lane (rows k0 .. N, N = the
+// right-hand side, at most 32 of them) with the row's panel entries in registers.  EVERY lane also loads the W x W
+// pivot block (broadcast loads) and factors it redundantly, so a lane finishes its own row of the panel
+// (u_c = a_c - sum_{q<c} u_q l_cq, l_c = u_c / d_c) without any exchange between lanes: the chain per pivot is
+// reciprocal -> quotient -> fma, no shuffle, no barrier.  The u / l columns of the rows below the panel go to the
+// 2 W scratch columns, one barrier, all owners apply the W rank-1 updates in ascending pivot order (the same fma
+// sequence per entry as the column path: bit-identical results), one barrier.
+#define SN_PW 4
+#ifdef B_FINE
+__device__ long long g_fine[8];
+#endif
+// correctly rounded reciprocal of a normal, finite d (pivots of an SPD matrix): MUFU seed (20 bits) and three
+// Newton steps, the last one from a 1-ulp approximation (Markstein).  Same bits as __drcp_rn on this range, a third
+// of its instructions and no slow-path branch.
+__device__ __forceinline__ double b_rcp(double d)
 {
-    double u0v[SN_EPTS], l0v[SN_EPTS], u1v[SN_EPTS], l1v[SN_EPTS], av[SN_EPTS];
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0); r = fma(r, e, r);
+    e = fma(-d, r, 1.0); r = fma(r, e, r);
+    e = fma(-d, r, 1.0); r = fma(r, e, r);
+    return r;
+}
+template <int W> __device__ __forceinline__ void b_panel_update(const unsigned (&ea)[SN_EPTS], const unsigned (&pu)[SN_EPTS],
+                                                                  const unsigned (&pl)[SN_EPTS], unsigned thr)
+{   // shared-memory bandwidth bound (10 accesses per entry): loads and fma's interleaved per entry measured faster than
+    // all loads first (347 vs 382 cycles per step alone on the SM, 441 vs 562 with four CTAs)
+    double av[SN_EPTS];
 #pragma unroll
-    for (int e = E0; e < SN_EPTS; e++) {
-        u0v[e] = b_lds<0>(pu[e]); l0v[e] = b_lds<8 * SN_W>(pl[e]);
-        u1v[e] = b_lds<16 * SN_W>(pu[e]); l1v[e] = b_lds<24 * SN_W>(pl[e]);
-        av[e] = b_lds<0>(ea[e]);
+    for (int e = 0; e < SN_EPTS; e++) av[e] = b_lds<0>(ea[e]);
+#pragma unroll
+    for (int e = 0; e < SN_EPTS; e++) {
+        { const double u0 = b_lds<0>(pu[e]), l0 = b_lds<8 * SN_W>(pl[e]); av[e] = fma(-u0, l0, av[e]); }
+        if (W > 1) { const double u1 = b_lds<16 * SN_W>(pu[e]), l1 = b_lds<24 * SN_W>(pl[e]); av[e] = fma(-u1, l1, av[e]); }
+        if (W > 2) { const double u2 = b_lds<32 * SN_W>(pu[e]), l2 = b_lds<40 * SN_W>(pl[e]); av[e] = fma(-u2, l2, av[e]); }
+        if (W > 3) { const double u3 = b_lds<48 * SN_W>(pu[e]), l3 = b_lds<56 * SN_W>(pl[e]); av[e] = fma(-u3, l3, av[e]); }
     }
 #pragma unroll
-    for (int e = E0; e < SN_EPTS; e++) av[e] = fma(-u0v[e], l0v[e], av[e]);
+    for (int e = 0; e < SN_EPTS; e++) b_sts_if(ea[e], av[e], pl[e] > thr);
+}
+// columns k0 .. k0 + W - 1 of the front (W <= nc - k0), executed by warp 0
+template <int W> __device__ __forceinline__ void b_panel_factor(double *L, double *xs, double *ucol, int f, int N, int base, int k0)
+{
+    const int t = threadIdx.x, rows = N - k0;                   // lane t: front row k0 + t; t == rows: the right-hand side
+    const int tc = t < rows ? t : rows;                           // lanes past the right-hand side repeat its work and store nothing
+    const bool live = t <= rows;
+    double *cq[W], *pa[W];                                        // column k0 + q, + front row;  this lane's entry of it
+    cq[0] = L + sn_col(base, k0, N);
 #pragma unroll
-    for (int e = E0; e < SN_EPTS; e++) av[e] = fma(-u1v[e], l1v[e], av[e]);
+    for (int q = 1; q < W; q++) cq[q] = cq[q - 1] + (N - k0 - q);
 #pragma unroll
-    for (int e = E0; e < SN_EPTS; e++) b_sts_if(ea[e], av[e], pl[e] > thr);
+    for (int q = 0; q < W; q++) pa[q] = tc < rows ? cq[q] + k0 + tc : xs + f + k0 + q;
+    double a[W], B[W][W];
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+#pragma unroll
+        for (int p = q; p < W; p++) B[p][q] = cq[q][k0 + p];
+        a[q] = *pa[q];                                            // lanes t < q read an unrelated entry: never used
+    }
+    double d[W], r[W], lb[W][W];
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+        d[q] = B[q][q];
+        r[q] = b_rcp(d[q]);
+#pragma unroll
+        for (int p = q + 1; p < W; p++) lb[p][q] = b_div(B[p][q], d[q], r[q]);
+#pragma unroll
+        for (int q2 = q + 1; q2 < W; q2++)
+#pragma unroll
+            for (int p = q2; p < W; p++) B[p][q2] = fma(-B[p][q], lb[q2][q], B[p][q2]);
+    }
+    double u[W], l[W];
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+        double acc = a[c];
+#pragma unroll
+        for (int q = 0; q < c; q++) acc = fma(-u[q], lb[c][q], acc);
+        u[c] = acc;
+        l[c] = b_div(acc, d[c], r[c]);
+    }
+    __syncwarp();                                                 // every lane has read the block before it is overwritten
+#pragma unroll
+    for (int c = 0; c < W; c++)
+        if (live && t >= c) *pa[c] = t == c ? d[c] : l[c];
+    if (live && t >= W) {
+        double *us = ucol + k0 + t;
+#pragma unroll
+        for (int c = 0; c < W; c++) { us[2 * c * SN_W] = u[c]; us[(2 * c + 1) * SN_W] = l[c]; }
+    }
 }
 __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double *L, double *xs, double *ucol, const int4 d0, const int4 d1)
 {
     const int tid = threadIdx.x;
     const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
     const int2 *emap = P.Emap2 + d1.y;
-    const int ne = d1.z, ept = (ne + BNT - 1) / BNT;
-    double *lcol = ucol + SN_W, *u1c = ucol + 2 * SN_W, *l1c = ucol + 3 * SN_W;
     const unsigned Ls = b_saddr(L), xss = b_saddr(xs), uc = b_saddr(ucol);
     unsigned ea[SN_EPTS], pu[SN_EPTS], pl[SN_EPTS];       // N < 32: at most 495 owned entries, 4 per thread
 #pragma unroll
@@ -382,64 +451,43 @@ __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double 
         ea[e] = em.y >= 0 ? Ls + 8u * (unsigned)em.y : xss + 8u * (unsigned)(~em.y);
         pu[e] = uc + 8u * (unsigned)(em.x & 255); pl[e] = uc + 8u * (unsigned)(em.x >> 8);
     }
-    int k = 0;
-    while (k < nc) {
-        const int pc = sn_col(base, k, N);
-#ifndef B_NO_PAIRS
-        if (k + 1 < nc) {
-            // two pivots per barrier pair: the lanes of warp 0 scale column k, apply its update to column k+1
-            // (and to the pivot d_{k+1}, redundantly in every lane) and scale column k+1 right away; the
-            // owners then apply both rank-1 updates.  Per entry the same fma's in the same order.
-            const int pc1 = sn_col(base, k + 1, N);
-            if (tid < N - k) {
-                const unsigned mask = 0xffffffffu >> (32 - (N - k));
-                const int i = k + 1 + tid;
-                double *pa0 = (i < N) ? L + pc + i : xs + f + k;
-                double *pa1 = (i < N) ? L + pc1 + i : xs + f + k + 1;          // lane 0: the pivot d_{k+1} itself
-                const double u0 = *pa0, dk = L[pc + k], w = L[pc + k + 1], a1 = *pa1, d1raw = L[pc1 + k + 1];
-                const double rk = __drcp_rn(dk);
-                const double l0 = b_div(u0, dk, rk), lw = b_div(w, dk, rk);
-                const double t1 = fma(-u0, lw, a1), d1v = fma(-w, lw, d1raw);
-                const double r1 = __drcp_rn(d1v);
-                const double l1 = b_div(t1, d1v, r1);
-                __syncwarp(mask);                               // every lane has read w before lane 0 overwrites it
-                ucol[i] = u0; lcol[i] = l0; *pa0 = l0;
-                if (tid == 0) *pa1 = d1v;
-                else { u1c[i] = t1; l1c[i] = l1; *pa1 = l1; }
-            }
-            __syncthreads();
-            // (skipping the slots whose columns are all finished -- four copies of this update behind a switch -- saved
-            // 5 % of the phase's cycles and lost 1 % of throughput to the larger code: one copy)
-            b_pair_update<0>(ea, pu, pl, uc + 8u * (unsigned)(k + 1));
-            __syncthreads();
-            k += 2;
-            continue;
-        }
+    int k0 = 0;
+    for (; k0 + SN_PW <= nc; k0 += SN_PW) {
+#ifdef B_FINE
+        const long long c0_ = clock64();
 #endif
-        if (tid < N - k) {                                  // rows k+1 .. N (N = right-hand side)
-            const int i = k + 1 + tid;
-            double *pa = (i < N) ? L + pc + i : xs + f + k;
-            const double u = *pa, dk = L[pc + k];
-            const double l = b_div(u, dk, __drcp_rn(dk));
-            ucol[i] = u; lcol[i] = l; *pa = l;
-        }
+        if (tid < 32) b_panel_factor<SN_PW>(L, xs, ucol, f, N, base, k0);
+#ifdef B_FINE
+        const long long c1_ = clock64();
+#endif
         __syncthreads();
-        const unsigned thr = uc + 8u * (unsigned)k;
-#pragma unroll
-        for (int h = 0; h < SN_EPTS; h += SN_EPTS) {
-            if (h < ept) {
-                double uv[SN_EPTS], lv[SN_EPTS], av[SN_EPTS];
-#pragma unroll
-                for (int e = 0; e < SN_EPTS; e++) { uv[e] = b_lds<0>(pu[h + e]); lv[e] = b_lds<8 * SN_W>(pl[h + e]); av[e] = b_lds<0>(ea[h + e]); }
-#pragma unroll
-                for (int e = 0; e < SN_EPTS; e++) av[e] = fma(-uv[e], lv[e], av[e]);
-#pragma unroll
-                for (int e = 0; e < SN_EPTS; e++) b_sts_if(ea[h + e], av[e], pl[h + e] > thr);
-            }
-        }
+#ifdef B_FINE
+        const long long c2_ = clock64();
+#endif
+        b_panel_update<SN_PW>(ea, pu, pl, uc + 8u * (unsigned)(k0 + SN_PW - 1));
+#ifdef B_FINE
+        const long long c3_ = clock64();
+#endif
         __syncthreads();
-        k++;
+#ifdef B_FINE
+        if (tid == 0) { const long long c4_ = clock64(); atomicAdd((unsigned long long *)&g_fine[0], (unsigned long long)(c1_ - c0_)); atomicAdd((unsigned long long *)&g_fine[1], (unsigned long long)(c2_ - c1_)); atomicAdd((unsigned long long *)&g_fine[2], (unsigned long long)(c3_ - c2_)); atomicAdd((unsigned long long *)&g_fine[3], (unsigned long long)(c4_ - c3_)); atomicAdd((unsigned long long *)&g_fine[4], 1ull); }
+#endif
     }
+    for (; k0 < nc; ) {                                          // the last nc mod SN_PW pivots: two, then one
+        if (k0 + 2 <= nc) {
+            if (tid < 32) b_panel_factor<2>(L, xs, ucol, f, N, base, k0);
+            __syncthreads();
+            b_panel_update<2>(ea, pu, pl, uc + 8u * (unsigned)(k0 + 1));
+            k0 += 2;
+        } else {
+            if (tid < 32) b_panel_factor<1>(L, xs, ucol, f, N, base, k0);
+            __syncthreads();
+            b_panel_update<1>(ea, pu, pl, uc + 8u * (unsigned)k0);
+            k0 += 1;
+        }
+        __syncthreads();
+    }
+    (void)nr;
 }
 __device__ B_FN void b_factor_fronts(const BatchPlan &P, double *L, double *xs, double *ucol)
 {
@@ -497,8 +545,11 @@ __device__ B_FN void b_factor_fronts(const BatchPlan &P, double *L, double *xs, 
         }
     }
 }
-// x = L^{-T} xs: lane c owns pivot column c of the front, lanes nc..N-1 carry the already final
-// entries of the rows below; same fma sequence per entry as b_backward (descending row order)
+// x = L^{-T} xs: lane c owns pivot column c of the front.  Rows below the pivot block are final (broadcast loads
+// from xs); the pivot block goes four rows per step: every lane fetches the four right-hand-side values (shuffles)
+// and the six L entries between those rows (broadcast loads), solves the 4 x 4 triangle redundantly and applies the
+// four fma's to its own column -- one shuffle latency per four rows instead of one per row.  Per entry the same fma
+// sequence as b_backward (descending row order): bit-identical.
 __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *xs)
 {
     const int lane = threadIdx.x & 31;
@@ -506,46 +557,35 @@ __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *
         const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
         const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
         const int *rows = (P.nSrow <= SN_ROWS_MAX ? s_rows : P.Srow) + d1.x;
-        const int mycol = sn_col(base, lane, N);
-        double v = 0.0;
-        if (lane < nc) v = xs[f + lane]; else if (lane < N) v = xs[rows[lane - nc]];
-#ifdef B_BWD_UNROLLED
-        double col[SN_NMAX];
-#pragma unroll
-        for (int i = 1; i < SN_NMAX; i++) col[i] = (i < N && lane < nc && lane < i) ? L[mycol + i] : 0.0;
-#pragma unroll
-        for (int i = SN_NMAX - 1; i >= 1; i--) {
-            if (i < N) {
-                const double xi = __shfl_sync(0xffffffffu, v, i);
-                if (lane < i && lane < nc) v = fma(-col[i], xi, v);
-            }
-        }
-#else
-        // rolled: the L entry of step i is loaded while the broadcast of x_i is in flight (its address does not
-        // depend on the chain); 30 unrolled steps with the column in registers were 300 instructions and 60 registers
-        const int cend = lane < nc ? lane : -1;                  // lane updates while i > lane
-#ifndef B_BWD_ONELOOP
-        {   // rows below the pivot block are final: their broadcasts read the initial values, not the chain
-            const double v0 = v;
-#pragma unroll 1
-            for (int i = N - 1; i >= nc; i--) {
-                const double lic = cend >= 0 ? L[mycol + i] : 0.0;
-                const double xi = __shfl_sync(0xffffffffu, v0, i);
-                if (cend >= 0) v = fma(-lic, xi, v);
-            }
+        const bool own = lane < nc;
+        const double *col = L + sn_col(base, own ? lane : 0, N);      // + front row i
+        double v = own ? xs[f + lane] : 0.0;
+#pragma unroll 4
+        for (int i = N - 1; i >= nc; i--) {
+            const double xi = xs[rows[i - nc]], lic = own ? col[i] : 0.0;
+            v = fma(-lic, xi, v);
         }
 #pragma unroll 1
-        for (int i = nc - 1; i >= 1; i--) {
-#else
-#pragma unroll 1
-        for (int i = N - 1; i >= 1; i--) {
-#endif
-            const double lic = i > cend && cend >= 0 ? L[mycol + i] : 0.0;
-            const double xi = __shfl_sync(0xffffffffu, v, i);
-            if (i > cend && cend >= 0) v = fma(-lic, xi, v);
+        for (int i0 = nc - 1; i0 >= 1; i0 -= 4) {
+            // rows i0, i0-1, i0-2, i0-3 (rows below 0 do not exist: their x and L entries read as zero)
+            const int i1 = i0 - 1, i2 = i0 - 2, i3 = i0 - 3;
+            const double *c1 = L + sn_col(base, i1, N), *c2 = L + sn_col(base, i2 > 0 ? i2 : 0, N), *c3 = L + sn_col(base, i3 > 0 ? i3 : 0, N);
+            const double l01 = c1[i0];
+            const double l02 = i2 >= 0 ? c2[i0] : 0.0, l12 = i2 >= 0 ? c2[i1] : 0.0;
+            const double l03 = i3 >= 0 ? c3[i0] : 0.0, l13 = i3 >= 0 ? c3[i1] : 0.0, l23 = i3 >= 0 ? c3[i2] : 0.0;
+            const double m0 = lane < i0 && own ? col[i0] : 0.0, m1 = lane < i1 && own ? col[i1] : 0.0;
+            const double m2 = lane < i2 && own ? col[i2] : 0.0, m3 = lane < i3 && own ? col[i3] : 0.0;
+            const double x0 = __shfl_sync(0xffffffffu, v, i0), v1 = __shfl_sync(0xffffffffu, v, i1);
+            const double v2 = __shfl_sync(0xffffffffu, v, i2 > 0 ? i2 : 0), v3 = __shfl_sync(0xffffffffu, v, i3 > 0 ? i3 : 0);
+            const double x1 = fma(-l01, x0, v1);
+            const double x2 = fma(-l12, x1, fma(-l02, x0, v2));
+            const double x3 = fma(-l23, x2, fma(-l13, x1, fma(-l03, x0, v3)));
+            if (lane < i0 && own) v = fma(-m0, x0, v);
+            if (lane < i1 && own) v = fma(-m1, x1, v);
+            if (lane < i2 && own) v = fma(-m2, x2, v);
+            if (lane < i3 && own) v = fma(-m3, x3, v);
         }
-#endif
-        if (lane < nc) xs[f + lane] = v;
+        if (own) xs[f + lane] = v;
         __syncwarp();
     }
 }
@@ -1125,7 +1165,7 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC Batch
 #undef TAKE
     V.K = p; p += P.karea;
     V.red = p; p += BNW * 8;
-    V.ucol = p; p += 4 * P.ucolw;
+    V.ucol = p; p += 2 * SN_PW * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
     if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
     if (P.nSrow <= SN_ROWS_MAX) for (int t = threadIdx.x; t < P.nSrow; t += BNT) s_rows[t] = P.Srow[t];
@@ -1427,7 +1467,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.eps_abs = s->eps_abs; P.eps_abs_in = s->eps_abs_in; P.eps_prim_inf = s->eps_prim_inf; P.eps_dual_inf = s->eps_dual_inf;
         P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
         P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
-        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 4 * (size_t)P.ucolw) + 2 * (size_t)m + 16;
+        b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * SN_PW * (size_t)P.ucolw) + 2 * (size_t)m + 16;
         if (b->smem > 227 * 1024) {
             qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
             break;
@@ -1436,6 +1476,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         int per_sm = 0, sms = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_solve, BNT, b->smem);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        { const char *ev = getenv("QPDO_BATCH_CTAS_PER_SM"); if (ev && atoi(ev) > 0) per_sm = std::min(per_sm, atoi(ev)); }   // occupancy experiments
         b->ctas = std::max(1, per_sm) * std::max(1, sms);
         if (cudaStreamCreateWithFlags(&b->st, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&b->st2, cudaStreamNonBlocking) != cudaSuccess) { qpdo_set_error("cudaStreamCreate failed"); break; }
         cudaEventCreate(&b->e0); cudaEventCreate(&b->e1);
@@ -1540,6 +1581,9 @@ extern "C" int qpdo_batch_timing(qpdo_batch *b, int count, double *cycles8)
     return 0;
 }
 
+#ifdef B_FINE
+extern "C" int qpdo_batch_fine(long long *out8) { return cudaMemcpyFromSymbol(out8, g_fine, sizeof(long long) * 8) == cudaSuccess ? 0 : -1; }
+#endif
 extern "C" int qpdo_batch_info(const qpdo_batch *b, int *smem_bytes, int *ctas, int *lnz, int *threads)
 {
     if (!b) return -3;
