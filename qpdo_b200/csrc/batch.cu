@@ -228,6 +228,26 @@ __device__ __forceinline__ double b_div(double u, double d, double r)
     return fma(fma(-q0, d, u), r, q0);
 }
 
+// correctly rounded reciprocal of a normal, finite d (pivots of an SPD matrix): MUFU seed (20 bits) and three
+// Newton steps, the last one from a 1-ulp approximation (Markstein).  Same bits as __drcp_rn on this range, a third
+// of its instructions and no slow-path branch.
+__device__ __forceinline__ double b_rcp(double d)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0); r = fma(r, e, r);
+    e = fma(-d, r, 1.0); r = fma(r, e, r);
+    e = fma(-d, r, 1.0); r = fma(r, e, r);
+    return r;
+}
+// a / d with the bits of the division operator: reciprocal + Markstein correction when both operands are normal
+// numbers of moderate exponent (|exponent| <= 500: no intermediate can overflow or underflow), the operator otherwise
+__device__ __forceinline__ double b_quot(double a, double d)
+{
+    const unsigned ea = ((unsigned)__double2hiint(a) & 0x7ff00000u) - 0x20b00000u, ed = ((unsigned)__double2hiint(d) & 0x7ff00000u) - 0x20b00000u;
+    if (ea <= 0x3e800000u && ed <= 0x3e800000u) return b_div(a, d, b_rcp(d));
+    return a / d;
+}
 __device__ __forceinline__ int koff(int j, int n) { return j * n - ((j * (j - 1)) >> 1) - j; }   // (i, j), i >= j, at koff(j) + i
 
 // K = Q + sigma I + A' diag(omega) A in the permuted packed lower triangle: the fused replacement
@@ -359,18 +379,6 @@ __device__ __forceinline__ void b_sts_if(unsigned a, double v, bool p)
 #ifdef B_FINE
 __device__ long long g_fine[8];
 #endif
-// correctly rounded reciprocal of a normal, finite d (pivots of an SPD matrix): MUFU seed (20 bits) and three
-// Newton steps, the last one from a 1-ulp approximation (Markstein).  Same bits as __drcp_rn on this range, a third
-// of its instructions and no slow-path branch.
-__device__ __forceinline__ double b_rcp(double d)
-{
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-    double e = fma(-d, r, 1.0); r = fma(r, e, r);
-    e = fma(-d, r, 1.0); r = fma(r, e, r);
-    e = fma(-d, r, 1.0); r = fma(r, e, r);
-    return r;
-}
 template <int W> __device__ __forceinline__ void b_panel_update(const unsigned (&ea)[SN_EPTS], const unsigned (&pu)[SN_EPTS],
                                                                   const unsigned (&pl)[SN_EPTS], unsigned thr)
 {   // shared-memory bandwidth bound (10 accesses per entry): loads and fma's interleaved per entry measured faster than
@@ -551,42 +559,80 @@ __device__ B_FN void b_factor_fronts(const BatchPlan &P, double *L, double *xs, 
 // four fma's to its own column -- one shuffle latency per four rows instead of one per row.  Per entry the same fma
 // sequence as b_backward (descending row order): bit-identical.
 __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *xs)
-{
+{   // requires the descriptor and row caches (nsuper <= SN_DESC_MAX, nSrow <= SN_ROWS_MAX): plain shared-memory loads
     const int lane = threadIdx.x & 31;
+    const unsigned Ls = b_saddr(L), xss = b_saddr(xs), rws = b_saddr(s_rows);
     for (int s = P.nsuper - 1; s >= 0; s--) {
-        const int4 d0 = sn_desc(P, s, 0), d1 = sn_desc(P, s, 1);
+#ifdef B_FINE
+        const long long t0_ = clock64();
+#endif
+        const int4 d0 = s_desc[2 * s], d1 = s_desc[2 * s + 1];
         const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
-        const int *rows = (P.nSrow <= SN_ROWS_MAX ? s_rows : P.Srow) + d1.x;
         const bool own = lane < nc;
-        const double *col = L + sn_col(base, own ? lane : 0, N);      // + front row i
-        double v = own ? xs[f + lane] : 0.0;
-#pragma unroll 4
-        for (int i = N - 1; i >= nc; i--) {
-            const double xi = xs[rows[i - nc]], lic = own ? col[i] : 0.0;
-            v = fma(-lic, xi, v);
-        }
+        const int lim = own ? lane : 64;                               // this lane's column takes the update of row i while lim < i
+        const int cl = own ? lane : nc - 1;                            // lanes past the pivot block repeat the last column's work and store nothing
+        const unsigned colb = Ls + 8u * (unsigned)sn_col(base, cl, N); // + 8 * front row
+        double v = b_lds<0>(xss + 8u * (unsigned)(f + cl));
+        {   // rows below the pivot block (final values), descending: x_i broadcast from xs[rows[i - nc]]
+            unsigned ra = rws + 4u * (unsigned)(d1.x + nr), ca = colb + 8u * (unsigned)N;
+            int k = nr;
 #pragma unroll 1
-        for (int i0 = nc - 1; i0 >= 1; i0 -= 4) {
-            // rows i0, i0-1, i0-2, i0-3 (rows below 0 do not exist: their x and L entries read as zero)
-            const int i1 = i0 - 1, i2 = i0 - 2, i3 = i0 - 3;
-            const double *c1 = L + sn_col(base, i1, N), *c2 = L + sn_col(base, i2 > 0 ? i2 : 0, N), *c3 = L + sn_col(base, i3 > 0 ? i3 : 0, N);
-            const double l01 = c1[i0];
-            const double l02 = i2 >= 0 ? c2[i0] : 0.0, l12 = i2 >= 0 ? c2[i1] : 0.0;
-            const double l03 = i3 >= 0 ? c3[i0] : 0.0, l13 = i3 >= 0 ? c3[i1] : 0.0, l23 = i3 >= 0 ? c3[i2] : 0.0;
-            const double m0 = lane < i0 && own ? col[i0] : 0.0, m1 = lane < i1 && own ? col[i1] : 0.0;
-            const double m2 = lane < i2 && own ? col[i2] : 0.0, m3 = lane < i3 && own ? col[i3] : 0.0;
-            const double x0 = __shfl_sync(0xffffffffu, v, i0), v1 = __shfl_sync(0xffffffffu, v, i1);
-            const double v2 = __shfl_sync(0xffffffffu, v, i2 > 0 ? i2 : 0), v3 = __shfl_sync(0xffffffffu, v, i3 > 0 ? i3 : 0);
+            for (; k >= 4; k -= 4) {
+                int r0, r1, r2, r3;
+                asm volatile("ld.shared.b32 %0, [%1+-4];" : "=r"(r0) : "r"(ra)); asm volatile("ld.shared.b32 %0, [%1+-8];" : "=r"(r1) : "r"(ra));
+                asm volatile("ld.shared.b32 %0, [%1+-12];" : "=r"(r2) : "r"(ra)); asm volatile("ld.shared.b32 %0, [%1+-16];" : "=r"(r3) : "r"(ra));
+                const double l0 = b_lds<-8>(ca), l1 = b_lds<-16>(ca), l2 = b_lds<-24>(ca), l3 = b_lds<-32>(ca);
+                const double x0 = b_lds<0>(xss + 8u * (unsigned)r0), x1 = b_lds<0>(xss + 8u * (unsigned)r1);
+                const double x2 = b_lds<0>(xss + 8u * (unsigned)r2), x3 = b_lds<0>(xss + 8u * (unsigned)r3);
+                v = fma(-l0, x0, v); v = fma(-l1, x1, v); v = fma(-l2, x2, v); v = fma(-l3, x3, v);
+                ra -= 16u; ca -= 32u;
+            }
+#pragma unroll 1
+            for (; k >= 1; k--) {
+                int r0;
+                asm volatile("ld.shared.b32 %0, [%1+-4];" : "=r"(r0) : "r"(ra));
+                const double l0 = b_lds<-8>(ca), x0 = b_lds<0>(xss + 8u * (unsigned)r0);
+                v = fma(-l0, x0, v);
+                ra -= 4u; ca -= 8u;
+            }
+        }
+#ifdef B_FINE
+        const long long t1_ = clock64();
+#endif
+        // pivot block, rows i0 .. i0-3 per step; am = &col[i0], a1..a3 = &L(i0, i0-1), &L(i0, i0-2), &L(i0, i0-3) as
+        // shared-space byte addresses, stepped without multiplications (column j-1 starts N - j entries before column j).
+        // A lane whose column does not take the update of a row multiplies by zero (the multiplier is selected off the chain).
+        int i0 = nc - 1, g = N - i0;
+        unsigned am = colb + 8u * (unsigned)i0;
+        unsigned a1 = Ls + 8u * (unsigned)(sn_col(base, i0, N) + i0) - 8u * (unsigned)g;
+#pragma unroll 1
+        for (; i0 >= 3; i0 -= 4) {
+            const unsigned a2 = a1 - 8u * (unsigned)(g + 1), a3 = a2 - 8u * (unsigned)(g + 2);
+            const double l01 = b_lds<0>(a1), l02 = b_lds<0>(a2), l12 = b_lds<-8>(a2);
+            const double l03 = b_lds<0>(a3), l13 = b_lds<-8>(a3), l23 = b_lds<-16>(a3);
+            double m0 = b_lds<0>(am), m1 = b_lds<-8>(am), m2 = b_lds<-16>(am), m3 = b_lds<-24>(am);
+            m0 = lim < i0 ? m0 : 0.0; m1 = lim < i0 - 1 ? m1 : 0.0; m2 = lim < i0 - 2 ? m2 : 0.0; m3 = lim < i0 - 3 ? m3 : 0.0;
+            const double x0 = __shfl_sync(0xffffffffu, v, i0), v1 = __shfl_sync(0xffffffffu, v, i0 - 1);
+            const double v2 = __shfl_sync(0xffffffffu, v, i0 - 2), v3 = __shfl_sync(0xffffffffu, v, i0 - 3);
             const double x1 = fma(-l01, x0, v1);
             const double x2 = fma(-l12, x1, fma(-l02, x0, v2));
             const double x3 = fma(-l23, x2, fma(-l13, x1, fma(-l03, x0, v3)));
-            if (lane < i0 && own) v = fma(-m0, x0, v);
-            if (lane < i1 && own) v = fma(-m1, x1, v);
-            if (lane < i2 && own) v = fma(-m2, x2, v);
-            if (lane < i3 && own) v = fma(-m3, x3, v);
+            v = fma(-m0, x0, v); v = fma(-m1, x1, v); v = fma(-m2, x2, v); v = fma(-m3, x3, v);
+            a1 = a3 - 8u * (unsigned)(2 * g + 7) - 32u; am -= 32u; g += 4;
+        }
+#pragma unroll 1
+        for (; i0 >= 1; i0--) {                                        // at most three single rows
+            double m0 = b_lds<0>(am);
+            m0 = lim < i0 ? m0 : 0.0;
+            const double x0 = __shfl_sync(0xffffffffu, v, i0);
+            v = fma(-m0, x0, v);
+            am -= 8u;
         }
         if (own) xs[f + lane] = v;
         __syncwarp();
+#ifdef B_FINE
+        if (lane == 0) { const long long t2_ = clock64(); atomicAdd((unsigned long long *)&g_fine[5], (unsigned long long)(t1_ - t0_)); atomicAdd((unsigned long long *)&g_fine[6], (unsigned long long)(t2_ - t1_)); atomicAdd((unsigned long long *)&g_fine[7], 1ull); }
+#endif
     }
 }
 
@@ -683,7 +729,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
                 if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
                 else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
                 delta[k] = dl; alpha[k] = al;
-                const double t = al / dl;
+                const double t = b_quot(al, dl);
                 const bool L = t > 0.0, Pp = dl > 0.0;
                 if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
                 if (L) { r3[2] += 1.0; kk = (unsigned long long)__double_as_longlong(t); }
@@ -706,7 +752,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
             if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
             else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
             delta[k] = dl; alpha[k] = al;
-            const double t = al / dl;
+            const double t = b_quot(al, dl);
             const bool L = t > 0.0, Pp = dl > 0.0;
             if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
             if (L) { r3[2] += 1.0; kk = (unsigned long long)__double_as_longlong(t); }
@@ -925,7 +971,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                 const double z = bclamp(w, l, u);
                 const double rpi = Ax + mu * (yb - y) - z;
                 V.rpi[i] = rpi;
-                const double Einv = scaled ? __drcp_rn(V.E[i]) : 1.0;
+                const double Einv = scaled ? b_rcp(V.E[i]) : 1.0;
                 double a = fabs(scaled ? Einv * rp : rp), bb = fabs(scaled ? Einv * rpi : rpi);
                 nr[0] = a > nr[0] ? a : nr[0]; nr[1] = bb > nr[1] ? bb : nr[1];
             }
@@ -936,7 +982,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                 V.df[i] = df;
                 const double rdi = df + V.Aty[i];
                 V.rdi[i] = rdi;
-                const double Dinv = scaled ? __drcp_rn(V.D[i]) : 1.0;
+                const double Dinv = scaled ? b_rcp(V.D[i]) : 1.0;
                 double a = fabs(scaled ? Dinv * rd : rd), bb = fabs(scaled ? Dinv * rdi : rdi);
                 nr[2] = a > nr[2] ? a : nr[2]; nr[3] = bb > nr[3] ? bb : nr[3];
             }
@@ -964,7 +1010,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                             s1[0] += (V.u[i] < lim) ? V.u[i] * dp : 0.0;
                             s1[0] += (V.l[i] > -lim) ? V.l[i] * dm : 0.0;
                         }
-                        FOR_N(i) { double v = V.Atdy[i]; if (scaled) { v = __drcp_rn(V.D[i]) * v; V.Atdy[i] = v; } v = fabs(v); mx[0] = v > mx[0] ? v : mx[0]; }
+                        FOR_N(i) { double v = V.Atdy[i]; if (scaled) { v = b_rcp(V.D[i]) * v; V.Atdy[i] = v; } v = fabs(v); mx[0] = v > mx[0] ? v : mx[0]; }
                         block_sum<1>(s1, red);
                         block_max<1>(mx, red);
                         if (mx[0] <= en && s1[0] <= -en) {
@@ -986,7 +1032,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                         int viol = 0, d1, d2;
                         FOR_M(k) {
                             double a = V.Adx[k];
-                            if (scaled) { a = __drcp_rn(V.E[k]) * a; V.Adx[k] = a; }
+                            if (scaled) { a = b_rcp(V.E[k]) * a; V.Adx[k] = a; }
                             const double lim = scaled ? V.E[k] * 1e20 : 1e20;
                             if ((V.u[k] < lim && a >= en) || (V.l[k] > -lim && a <= -en)) viol = 1;
                         }
@@ -1080,7 +1126,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             else mode = 2;
             FOR_M(i) {      // row weights embodied in the factor + "dy" = (I+P) res_prim_in ./ mu (newton.c:37-40)
                 const int a = V.act[i], o = V.acto[i];
-                const double mui = V.mu[i], inv = __drcp_rn(mui);
+                const double mui = V.mu[i], inv = b_rcp(mui);
                 double om;
                 if (mode == 0) om = a ? inv : 0.0;
                 else if (mode == 1) { om = V.om[i]; if (a && !o) om = om + inv; if (!a && o) om = om - inv; }
@@ -1101,7 +1147,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             if (P.mode == 1) {
                 b_factor_fronts(P, V.K, V.tn, V.ucol);
                 B_TICK(4)
-                if (tid < 32) { if (P.max_front <= SN_NMAX) b_backward_sn(P, V.K, V.tn); else b_backward_fronts(P, V.K, V.tn); }
+                if (tid < 32) { if (P.max_front <= SN_NMAX && P.nsuper <= SN_DESC_MAX && P.nSrow <= SN_ROWS_MAX) b_backward_sn(P, V.K, V.tn); else b_backward_fronts(P, V.K, V.tn); }
                 __syncthreads();
             } else {
                 b_factor_forward(P, V.K, V.tn);
@@ -1114,7 +1160,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             b_spmv_A(P, V.Av, V.dx, V.Adx);
             __syncthreads();
             if (proximal) { FOR_N(i) V.Qdx[i] = V.Qdx[i] + sigma * V.dx[i]; }
-            FOR_M(i) { if (V.act[i]) { const double mui = V.mu[i]; V.dy[i] = V.dy[i] + b_div(V.Adx[i], mui, __drcp_rn(mui)); } }
+            FOR_M(i) { if (V.act[i]) { const double mui = V.mu[i]; V.dy[i] = V.dy[i] + b_div(V.Adx[i], mui, b_rcp(mui)); } }
             __syncthreads();
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
             __syncthreads();

@@ -32,3 +32,5 @@ if hasattr(bt.lib, "qpdo_batch_fine"):
     bt.lib.qpdo_batch_fine(f8)
     npan = max(1, f8[4])
     print("fine (warp 0 of CTA, per W=4 panel step): phase A %.0f, barrier %.0f, phase B %.0f, barrier %.0f cycles; %d panels" % (f8[0] / npan, f8[1] / npan, f8[2] / npan, f8[3] / npan, npan))
+    nf = max(1, f8[7])
+    print("fine backward per front: prologue + rows below %.0f, pivot-block steps %.0f cycles; %d fronts" % (f8[5] / nf, f8[6] / nf, nf))
