@@ -129,6 +129,10 @@ int  qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const double *Qdx, 
                               const double *Adx, const double *w, const double *l, const double *u,
                               double *tau);
 
+/* measured FP64 peaks of `device` (< 0: current), TFLOP/s: register-resident mma.sync.m8n8k4.f64 (DMMA) and DFMA
+ * loops over all SMs, best of four timed launches.  The roofline denominators of the numeric factorization. */
+int  qpdo_dev_measure_fp64(int device, double *dmma_tflops, double *dfma_tflops);
+
 #ifdef __cplusplus
 }
 #endif
