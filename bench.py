@@ -349,6 +349,11 @@ def run_c5(args, dist):
         if rc:
             raise RuntimeError("qpdo_batch_solve failed: %s" % bt.lib.qpdo_dev_last_error().decode())
 
+    # work-queue order: longest instance first by the iteration counts of the previous solve of the same batch (the
+    # receding-horizon pattern the batch entry exists for); the warm-up steps leave that order on the device.  The
+    # natural-order figure of the same launch is reported beside it (`kernel_ms_natural_order`).
+    nat_ms = [step_device() for _ in range(2)][-1]
+    bt.set_adaptive_order(not args.natural_order)
     for _ in range(max(args.warmup, 3)):
         step_device()
     torch.cuda.synchronize(); dist.barrier()
@@ -417,6 +422,8 @@ def run_c5(args, dist):
            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
            "config": c5_config(B, n, m, nnzA, dist.world),
            "kernel_ms_per_step": k_ms, "kernel_qp_per_s": B / (k_ms * 1e-3),
+           "kernel_ms_natural_order": dist.reduce([nat_ms], "max")[0],
+           "queue_order": "natural" if args.natural_order else "longest first, from the iteration counts of the previous step (qpdo_batch_set_adaptive_order); results do not depend on it",
            "batch_kernel": dict(info, mean_iterations=total_iter / B),
            "result": {"solved": int((allsum["status_val"] == 1).sum()), "primal_infeasible": int((allsum["status_val"] == -3).sum()),
                       "dual_infeasible": int((allsum["status_val"] == -4).sum()), "max_iter_reached": int((allsum["status_val"] == -2).sum()),
@@ -649,6 +656,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--size", type=int, default=0, help="c3: grid N (default 300); c5: batch size (default 65536); c4: n (default 200000)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--natural-order", action="store_true", help="c5: pull the work queue in instance order (no adaptive order)")
     ap.add_argument("--no-kkt", action="store_true", help="c5 at one GPU: leave the c3 record (`kkt`) out of the line")
     ap.add_argument("--ref-path-steps", type=int, default=0, help="c4 reference leg: only the first k path steps")
     ap.add_argument("--max-iter", type=int, default=0, help="c3: cap the loop passes per solve (profiling runs)")

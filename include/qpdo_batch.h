@@ -64,6 +64,22 @@ int  qpdo_batch_solve_device(qpdo_batch *b, int count, const double *dQx, const 
                              double *dx, double *dy, qpdo_batch_summary *dsummary,
                              unsigned char *dactive, int sync, float *kernel_ms);
 
+/* One process, `ngpu` GPUs of one box: batches[g] = a batch created on device g with the same pattern and settings.
+ * Instance i goes to GPU floor(i * ngpu / count) (contiguous blocks); every block runs through its
+ * GPU's chunked copy / kernel pipeline, all GPUs concurrently; buffers and results exactly as qpdo_batch_solve.
+ * There is no inter-GPU traffic (the summaries of all blocks land in the caller's one array); a multi-process job
+ * gathers them with one all-gather instead (bench.py). */
+int  qpdo_batch_solve_multi(qpdo_batch *const *batches, int ngpu, int count, const double *Qx, const double *Ax,
+                            const double *q, const double *l, const double *u, const double *c,
+                            const double *x0, const double *y0,
+                            double *x, double *y, qpdo_batch_summary *summary, unsigned char *active_set);
+
+/* Work-queue order.  on != 0: every solve that writes summaries also leaves, on the device, the order "longest
+ * instance first" by the iteration counts it just produced; the next solve of the SAME number of instances pulls its
+ * queue in that order (a receding-horizon loop re-solves similar problems; the ragged tail of a launch is set by
+ * where the longest instances start).  Results do not depend on the order.  Default: off (natural order). */
+int  qpdo_batch_set_adaptive_order(qpdo_batch *b, int on);
+
 /* Convenience for callers holding the reference's own structs: `count` QPDOData problems
  * (include/types.h:81-90) that share one pattern; returns -4 if they do not.  Creates a batch,
  * solves, destroys.  x / y: arrays of `count` host pointers (QPDOSolution.x / .y) or NULL. */

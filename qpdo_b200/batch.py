@@ -39,6 +39,8 @@ def _declare(lib):
     lib.qpdo_batch_solve_device.argtypes = [vp, C.c_int] + [vp] * 12 + [C.c_int, C.POINTER(C.c_float)]
     lib.qpdo_batch_info.argtypes = [vp, _pi, _pi, _pi, _pi]
     lib.qpdo_batch_solve_data.argtypes = [vp, C.c_int, C.POINTER(capi.QPDOSettings), vp, vp, vp, C.c_int]
+    lib.qpdo_batch_solve_multi.argtypes = [C.POINTER(vp), C.c_int, C.c_int] + [_pd] * 10 + [vp, vp]
+    lib.qpdo_batch_set_adaptive_order.argtypes = [vp, C.c_int]
     lib.qpdo_dev_last_error.restype = C.c_char_p
     return lib
 
@@ -110,6 +112,10 @@ class Batch(object):
             raise RuntimeError("qpdo_batch_solve_device failed (%d): %s" % (rc, self.lib.qpdo_dev_last_error().decode()))
         return ms.value
 
+    def set_adaptive_order(self, on=True):
+        """longest-first queue order from the iteration counts of the previous solve (include/qpdo_batch.h)"""
+        self.lib.qpdo_batch_set_adaptive_order(self.h, 1 if on else 0)
+
     def destroy(self):
         if getattr(self, "h", None):
             self.lib.qpdo_batch_destroy(self.h)
@@ -130,3 +136,20 @@ def from_mpc(batch, capacity=None, settings=None, device=-1):
     bt = Batch(n, m, Qp, Qi, batch["Ap"], batch["Ai"], capacity or B, settings, device)
     Qx = np.tile(batch["Qd"], (B, 1))
     return bt, (Qx, batch["Ax"], batch["q"], batch["l"], batch["u"])
+
+
+def solve_multi(batches, Qx, Ax, q, l, u, c=None, x0=None, y0=None, want_active=True):
+    """qpdo_batch_solve_multi: one process, one Batch per GPU, HOST buffers in, host results out."""
+    f = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+    Qx, Ax, q, l, u, c, x0, y0 = map(f, (Qx, Ax, q, l, u, c, x0, y0))
+    b0 = batches[0]
+    count = q.shape[0]
+    x = np.empty((count, b0.n)); y = np.empty((count, b0.m))
+    summ = np.zeros(count, dtype=SUMMARY_DTYPE)
+    act = np.zeros((count, b0.m), dtype=np.uint8) if want_active else None
+    hs = (C.c_void_p * len(batches))(*[bt.h for bt in batches])
+    rc = b0.lib.qpdo_batch_solve_multi(hs, len(batches), count, _dp(Qx), _dp(Ax), _dp(q), _dp(l), _dp(u), _dp(c), _dp(x0), _dp(y0),
+                                       _dp(x), _dp(y), summ.ctypes.data, None if act is None else act.ctypes.data)
+    if rc:
+        raise RuntimeError("qpdo_batch_solve_multi failed (%d): %s" % (rc, b0.lib.qpdo_dev_last_error().decode()))
+    return x, y, summ, act

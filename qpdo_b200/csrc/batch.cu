@@ -101,6 +101,7 @@ struct BatchIO {
     unsigned char *active;
     int count;
     int *next;                               // work queue head
+    const int *order;                        // the k-th pull of the queue takes instance order[k] (null: k itself)
     long long *timing;                       // [count][8] clock64 cycles per phase (diagnostics) or NULL
 };
 
@@ -885,14 +886,26 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
     for (int k = tid; k < P.nnzA; k += BNT) V.Av[k] = B_LDS_IN(io.Ax + (size_t)b * P.nnzA + k);
     for (int k = tid; k < P.nnzQ; k += BNT) V.Qv[k] = B_LDS_IN(io.Qx + (size_t)b * P.nnzQ + k);
     FOR_N(i) { V.q[i] = B_LDS_IN(io.q + (size_t)b * n + i); V.x[i] = 0.0; V.xbar[i] = 0.0; V.Qx[i] = 0.0; V.Aty[i] = 0.0; V.D[i] = 1.0; V.dx[i] = 0.0; }
+    int bad_bounds = 0;
     FOR_M(i) {
         double lo = B_LDS_IN(io.l + (size_t)b * m + i), hi = B_LDS_IN(io.u + (size_t)b * m + i);
+        bad_bounds |= lo > hi;                                        // validate_data (src/validate.c:19-28)
         V.l[i] = lo > -B_INFTY ? lo : -B_INFTY; V.u[i] = hi < B_INFTY ? hi : B_INFTY;
         V.y[i] = 0.0; V.ybar[i] = 0.0; V.Ax[i] = 0.0; V.E[i] = 1.0; V.om[i] = 0.0; V.dy[i] = 0.0; V.rpo[i] = 0.0;
         V.act[i] = 0; V.acto[i] = 0;
     }
     double c = 1.0, cinv = 1.0;
-    __syncthreads();
+    if (__syncthreads_or(bad_bounds)) {                               // qpdo_setup would return NULL: status QPDO_ERROR, nothing solved
+        if (io.x) { FOR_N(i) io.x[(size_t)b * n + i] = 0.0; }
+        if (io.y) { FOR_M(i) io.y[(size_t)b * m + i] = 0.0; }
+        if (io.active) { FOR_M(i) io.active[(size_t)b * m + i] = 0; }
+        if (io.summary && tid == 0) {
+            qpdo_batch_summary s;
+            s.status_val = QPDO_ERROR; s.iterations = 0; s.oterations = 0; s.n_active = 0; s.objective = 0.0; s.res_prim_norm = 0.0; s.res_dual_norm = 0.0;
+            io.summary[b] = s;
+        }
+        return;
+    }
     // ---- scale_data (src/scaling.c:24-91): Ruiz sweeps on A, Q <- DQD, q <- Dq, cost scaling
     if (scaled) {
         for (int it = 0; it < P.scaling; it++) {
@@ -1226,9 +1239,32 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC Batch
         __syncthreads();
         if (threadIdx.x == 0) s_b = atomicAdd(io.next, 1);
         __syncthreads();
-        const int b = s_b;
-        if (b >= io.count) break;
+        if (s_b >= io.count) break;
+        const int b = io.order ? io.order[s_b] : s_b;
         b_solve_instance(P, io, V, b);
+    }
+}
+
+// Queue order for the NEXT solve of the same instances: longest first, by the iteration counts of the solve that
+// just finished (counting sort, one CTA; ties in arbitrary order -- the order only schedules, results do not depend
+// on it).  A receding-horizon loop re-solves similar problems, and the ragged tail of a launch is set by where the
+// longest instances start.
+#define B_ORDER_BINS 4096
+__global__ void __launch_bounds__(1024) k_batch_order(const qpdo_batch_summary *summary, int count, int *order)
+{
+    __shared__ int bins[B_ORDER_BINS];
+    for (int t = threadIdx.x; t < B_ORDER_BINS; t += blockDim.x) bins[t] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        int it = summary[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
+        atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1);                 // descending
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { int acc = 0; for (int t = 0; t < B_ORDER_BINS; t++) { const int c = bins[t]; bins[t] = acc; acc += c; } }
+    __syncthreads();
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        int it = summary[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
+        order[atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1)] = i;
     }
 }
 
@@ -1246,6 +1282,8 @@ struct qpdo_batch {
     qpdo_batch_summary *dsum = nullptr;
     unsigned char *dact = nullptr;
     int *next = nullptr;
+    int *dorder = nullptr;            // [capacity] queue order per launch range (relative indices), valid when order_count > 0
+    int adaptive = 0, order_count = 0, order_chunks = 0;
     long long *timing = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
 };
@@ -1530,7 +1568,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         if (b_alloc(b, &b->dQx, cap * nnzQ) || b_alloc(b, &b->dAx, cap * nnzA) || b_alloc(b, &b->dq, cap * n) || b_alloc(b, &b->dl, cap * m) ||
             b_alloc(b, &b->du, cap * m) || b_alloc(b, &b->dc, cap) || b_alloc(b, &b->dx0, cap * n) || b_alloc(b, &b->dy0, cap * m) ||
             b_alloc(b, &b->dx, cap * n) || b_alloc(b, &b->dy, cap * m) || b_alloc(b, &b->dsum, cap) || b_alloc(b, &b->dact, cap * m) ||
-            b_alloc(b, &b->next, 2))
+            b_alloc(b, &b->next, 2) || b_alloc(b, &b->dorder, cap))
             break;
         rc = 0;
     } while (0);
@@ -1540,7 +1578,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
     return 0;
 }
 
-static int batch_launch(qpdo_batch *b, cudaStream_t st, int *next, int first, int count, const double *dQx, const double *dAx,
+static int batch_launch(qpdo_batch *b, cudaStream_t st, int *next, int first, int count, bool use_order, const double *dQx, const double *dAx,
                         const double *dq, const double *dl, const double *du, const double *dc, const double *dx0, const double *dy0,
                         double *dx, double *dy, qpdo_batch_summary *dsummary, unsigned char *dactive)
 {   // instances first .. first + count - 1 of the given (instance-major) device arrays
@@ -1551,9 +1589,14 @@ static int batch_launch(qpdo_batch *b, cudaStream_t st, int *next, int first, in
     io.x = dx ? dx + o * n : nullptr; io.y = dy ? dy + o * m : nullptr; io.summary = dsummary ? dsummary + o : nullptr;
     io.active = dactive ? dactive + o * m : nullptr; io.count = count; io.next = next;
     io.timing = b->timing ? b->timing + o * 8 : nullptr;
+    io.order = use_order ? b->dorder + o : nullptr;
     CUDA_OK(cudaMemsetAsync(next, 0, sizeof(int), st));
     k_batch_solve<<<std::min(count, b->ctas), BNT, b->smem, st>>>(b->P, io);
     CUDA_OK(cudaGetLastError());
+    if (b->adaptive && dsummary) {
+        k_batch_order<<<1, 1024, 0, st>>>(dsummary + o, count, b->dorder + o);
+        CUDA_OK(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -1563,11 +1606,15 @@ extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *d
                                        float *kernel_ms)
 {
     if (!b || count < 0 || !dQx || !dAx || !dq || !dl || !du) { qpdo_set_error("qpdo_batch_solve_device: bad arguments"); return -3; }
+    // the per-instance scratch of the library (queue order, phase accounting) is sized for `capacity` instances
+    if (count > b->capacity) { qpdo_set_error("qpdo_batch_solve_device: count %d exceeds the capacity %d the batch was created with", count, b->capacity); return -3; }
     if (count == 0) return 0;
     CUDA_OK(cudaSetDevice(b->device));
+    const bool use_order = b->adaptive && b->order_count == count && b->order_chunks == 1;
     if (kernel_ms) CUDA_OK(cudaEventRecord(b->e0, b->st));
-    if (batch_launch(b, b->st, b->next, 0, count, dQx, dAx, dq, dl, du, dc, dx0, dy0, dx, dy, dsummary, dactive)) return -1;
+    if (batch_launch(b, b->st, b->next, 0, count, use_order, dQx, dAx, dq, dl, du, dc, dx0, dy0, dx, dy, dsummary, dactive)) return -1;
     if (kernel_ms) CUDA_OK(cudaEventRecord(b->e1, b->st));
+    if (b->adaptive && dsummary) { b->order_count = count; b->order_chunks = 1; } else b->order_count = 0;
     if (sync || kernel_ms) {
         CUDA_OK(cudaStreamSynchronize(b->st));
         if (kernel_ms) CUDA_OK(cudaEventElapsedTime(kernel_ms, b->e0, b->e1));
@@ -1575,17 +1622,27 @@ extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *d
     return 0;
 }
 
-extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, const double *Ax, const double *q, const double *l,
-                                const double *u, const double *c, const double *x0, const double *y0, double *x, double *y,
-                                qpdo_batch_summary *summary, unsigned char *active_set)
+// chunks of a host-buffer solve: enough of them that the first host->device and the last device->host copy are a
+// small part of the call, few enough that every chunk still fills the resident CTAs several times over
+static int batch_chunks(const qpdo_batch *b, int count)
 {
-    if (!b || count < 0 || count > b->capacity || !Qx || !Ax || !q || !l || !u) { qpdo_set_error("qpdo_batch_solve: bad arguments (count > capacity?)"); return -3; }
-    if (count == 0) return 0;
+    int nchunk = count / (3 * b->ctas);
+    return nchunk < 1 ? 1 : nchunk > 8 ? 8 : nchunk;
+}
+
+// issue (asynchronously, on the batch's two streams) the copies and launches of instances [0, count) of the given
+// HOST arrays; batch_solve_wait joins them
+static int batch_solve_issue(qpdo_batch *b, int count, const double *Qx, const double *Ax, const double *q, const double *l,
+                             const double *u, const double *c, const double *x0, const double *y0, double *x, double *y,
+                             qpdo_batch_summary *summary, unsigned char *active_set)
+{
     CUDA_OK(cudaSetDevice(b->device));
     const size_t n = b->n, m = b->m, D = sizeof(double);
     // chunks alternate between two streams: the host->device copy of chunk k+1 and the device->host copy of
-    // chunk k-1 overlap the kernel of chunk k (with pinned host buffers; pageable ones just serialise)
-    const int nchunk = count >= 8 * b->ctas ? 8 : 1;
+    // chunk k-1 overlap the kernel of chunk k (with pinned host buffers; pageable ones just serialise), and the
+    // ragged tail of one chunk's launch is filled by the head of the next
+    const int nchunk = batch_chunks(b, count);
+    const bool use_order = b->adaptive && b->order_count == count && b->order_chunks == nchunk;
     for (int k = 0; k < nchunk; k++) {
         const int lo = (int)((long)count * k / nchunk), hi = (int)((long)count * (k + 1) / nchunk), cn = hi - lo;
         if (cn <= 0) continue;
@@ -1599,7 +1656,7 @@ extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, cons
         if (c) CUDA_OK(cudaMemcpyAsync(b->dc + o, c + o, D * cn, cudaMemcpyHostToDevice, st));
         if (x0) CUDA_OK(cudaMemcpyAsync(b->dx0 + o * n, x0 + o * n, D * cn * n, cudaMemcpyHostToDevice, st));
         if (y0 && m) CUDA_OK(cudaMemcpyAsync(b->dy0 + o * m, y0 + o * m, D * cn * m, cudaMemcpyHostToDevice, st));
-        if (batch_launch(b, st, b->next + (k & 1), lo, cn, b->dQx, b->dAx, b->dq, b->dl, b->du, c ? b->dc : nullptr, x0 ? b->dx0 : nullptr,
+        if (batch_launch(b, st, b->next + (k & 1), lo, cn, use_order, b->dQx, b->dAx, b->dq, b->dl, b->du, c ? b->dc : nullptr, x0 ? b->dx0 : nullptr,
                          (y0 && m) ? b->dy0 : nullptr, b->dx, b->dy, b->dsum, b->dact))
             return -1;
         if (x) CUDA_OK(cudaMemcpyAsync(x + o * n, b->dx + o * n, D * cn * n, cudaMemcpyDeviceToHost, st));
@@ -1607,9 +1664,61 @@ extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, cons
         if (summary) CUDA_OK(cudaMemcpyAsync(summary + o, b->dsum + o, sizeof(qpdo_batch_summary) * cn, cudaMemcpyDeviceToHost, st));
         if (active_set && m) CUDA_OK(cudaMemcpyAsync(active_set + o * m, b->dact + o * m, (size_t)cn * m, cudaMemcpyDeviceToHost, st));
     }
+    if (b->adaptive) { b->order_count = count; b->order_chunks = nchunk; } else b->order_count = 0;
+    return 0;
+}
+static int batch_solve_wait(qpdo_batch *b)
+{
+    CUDA_OK(cudaSetDevice(b->device));
     cudaError_t e = cudaStreamSynchronize(b->st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(b->st2);
     if (e != cudaSuccess) { qpdo_set_error("batch kernel failed: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+extern "C" int qpdo_batch_solve(qpdo_batch *b, int count, const double *Qx, const double *Ax, const double *q, const double *l,
+                                const double *u, const double *c, const double *x0, const double *y0, double *x, double *y,
+                                qpdo_batch_summary *summary, unsigned char *active_set)
+{
+    if (!b || count < 0 || count > b->capacity || !Qx || !Ax || !q || !l || !u) { qpdo_set_error("qpdo_batch_solve: bad arguments (count > capacity?)"); return -3; }
+    if (count == 0) return 0;
+    if (batch_solve_issue(b, count, Qx, Ax, q, l, u, c, x0, y0, x, y, summary, active_set)) return -1;
+    return batch_solve_wait(b);
+}
+
+// One process, several GPUs (SURVEY.md 8(b) "device/GPU-count selection", 8(e)): instance i goes to GPU floor(i * G / count),
+// contiguous blocks, every block through that GPU's own chunked pipeline, all GPUs in flight at once.  No inter-GPU
+// traffic: the summaries of all blocks land in the caller's one host array.
+extern "C" int qpdo_batch_solve_multi(qpdo_batch *const *batches, int ngpu, int count, const double *Qx, const double *Ax,
+                                      const double *q, const double *l, const double *u, const double *c, const double *x0,
+                                      const double *y0, double *x, double *y, qpdo_batch_summary *summary, unsigned char *active_set)
+{
+    if (!batches || ngpu <= 0 || count < 0 || !Qx || !Ax || !q || !l || !u) { qpdo_set_error("qpdo_batch_solve_multi: bad arguments"); return -3; }
+    for (int g = 0; g < ngpu; g++) {
+        const qpdo_batch *b = batches[g];
+        if (!b || b->n != batches[0]->n || b->m != batches[0]->m || b->nnzA != batches[0]->nnzA || b->nnzQ != batches[0]->nnzQ) { qpdo_set_error("qpdo_batch_solve_multi: batch %d is null or has another shape", g); return -3; }
+        const long lo = ((long)count * g + ngpu - 1) / ngpu, hi = ((long)count * (g + 1) + ngpu - 1) / ngpu;
+        if (hi - lo > b->capacity) { qpdo_set_error("qpdo_batch_solve_multi: block %d holds %ld instances, capacity %d", g, hi - lo, b->capacity); return -3; }
+    }
+    int rc = 0, issued = 0;
+    for (int g = 0; g < ngpu && !rc; g++) {
+        qpdo_batch *b = batches[g];
+        const size_t lo = (size_t)(((long)count * g + ngpu - 1) / ngpu), hi = (size_t)(((long)count * (g + 1) + ngpu - 1) / ngpu), n = b->n, m = b->m;
+        issued = g + 1;
+        if (hi == lo) continue;
+        rc = batch_solve_issue(b, (int)(hi - lo), Qx + lo * b->nnzQ, Ax + lo * b->nnzA, q + lo * n, l + lo * m, u + lo * m, c ? c + lo : nullptr,
+                               x0 ? x0 + lo * n : nullptr, y0 ? y0 + lo * m : nullptr, x ? x + lo * n : nullptr, y ? y + lo * m : nullptr,
+                               summary ? summary + lo : nullptr, active_set ? active_set + lo * m : nullptr);
+    }
+    for (int g = 0; g < issued; g++) if (batch_solve_wait(batches[g])) rc = -1;
+    return rc;
+}
+
+extern "C" int qpdo_batch_set_adaptive_order(qpdo_batch *b, int on)
+{
+    if (!b) return -3;
+    b->adaptive = on ? 1 : 0;
+    b->order_count = 0;
     return 0;
 }
 

@@ -54,9 +54,10 @@ void qpdo_profile_collect(qpdo_dev *d)
     d->ev_used.clear();
     d->ev_next = 0;
 }
-extern "C" int qpdo_dev_set_profiling(qpdo_dev *d, int on) { qpdo_profile_collect(d); d->profiling = on; return 0; }
+extern "C" int qpdo_dev_set_profiling(qpdo_dev *d, int on) { if (d) cudaSetDevice(d->device); qpdo_profile_collect(d); d->profiling = on; return 0; }
 extern "C" int qpdo_dev_get_profile(qpdo_dev *d, qpdo_dev_profile *out, int reset)
 {
+    if (d) cudaSetDevice(d->device);
     qpdo_profile_collect(d);
     *out = d->prof;
     if (reset) d->prof = qpdo_dev_profile();
@@ -339,6 +340,7 @@ extern "C" void qpdo_dev_destroy(qpdo_dev *d)
 extern "C" int qpdo_dev_get_scaling(qpdo_dev *d, double *D, double *Dinv, double *E, double *Einv, double *c,
                                     double *cinv, double *norm_q)
 {
+    if (d) cudaSetDevice(d->device);
     const size_t nb = sizeof(double) * d->n, mb = sizeof(double) * d->m;
     if (D) CUDA_OK(cudaMemcpyAsync(D, d->D, nb, cudaMemcpyDeviceToHost, d->st));
     if (Dinv) CUDA_OK(cudaMemcpyAsync(Dinv, d->Dinv, nb, cudaMemcpyDeviceToHost, d->st));
@@ -358,6 +360,7 @@ extern "C" int qpdo_dev_get_scaling(qpdo_dev *d, double *D, double *Dinv, double
 // The iterates are left as they are, like in the reference: callers warm-start afterwards.
 extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
 {
+    if (d) cudaSetDevice(d->device);
     if (extra_iters <= 0) return 0;
     if (d->scaling_iters <= 0) {      // the reference dereferences work->scaling == NULL here (qpdo.c:498): an error instead
         qpdo_set_error("qpdo_update_settings: scaling cannot be switched on after a setup with scaling = 0");
@@ -396,6 +399,7 @@ extern "C" int qpdo_dev_rescale(qpdo_dev *d, int extra_iters)
 
 extern "C" int qpdo_dev_get_symbolic_info(qpdo_dev *d, qpdo_dev_symbolic_info *o)
 {
+    if (d) cudaSetDevice(d->device);
     const qpdo_symbolic *S = d->F.S;
     if (!S) { memset(o, 0, sizeof *o); o->analyze_seconds = d->analyze_seconds; return 0; }      // dynamic pattern, nothing factored yet
     o->nsuper = S->nsuper; o->nlevel = S->nlevel; o->max_front = S->max_front; o->max_nc = S->max_nc;

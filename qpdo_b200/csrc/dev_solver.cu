@@ -434,6 +434,7 @@ static int objective_dev(qpdo_dev *d, int proximal, double *out_dev)
 
 extern "C" int qpdo_dev_objective(qpdo_dev *d, int proximal, double c_const, double *objective)
 {
+    if (d) cudaSetDevice(d->device);
     objective_dev(d, proximal, d->red + 8);
     double v = 0;
     CUDA_OK(cudaMemcpyAsync(&v, d->red + 8, sizeof(double), cudaMemcpyDeviceToHost, d->st));
@@ -446,6 +447,7 @@ extern "C" int qpdo_dev_objective(qpdo_dev *d, int proximal, double c_const, dou
 extern "C" int qpdo_dev_warm_start(qpdo_dev *d, const double *x, const double *y, double sigma, int proximal,
                                    double mu_min, double *objective)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m, scaled = d->scaling_iters > 0;
     (void)mu_min;
     k_set_sigma<<<1, 1, 0, d->st>>>(d->sc, sigma, 0);
@@ -489,6 +491,7 @@ extern "C" int qpdo_dev_warm_start(qpdo_dev *d, const double *x, const double *y
 
 extern "C" int qpdo_dev_begin_solve(qpdo_dev *d, double sigma)
 {
+    if (d) cudaSetDevice(d->device);
     CUDA_OK(cudaMemsetAsync(d->sc, 0, sizeof(qpdo_dev_scalars), d->st));
     k_set_sigma<<<1, 1, 0, d->st>>>(d->sc, sigma, 1);
     if (d->m) CUDA_OK(cudaMemsetAsync(d->act_old, 0, sizeof(int) * d->m, d->st));
@@ -498,6 +501,7 @@ extern "C" int qpdo_dev_begin_solve(qpdo_dev *d, double sigma)
 
 extern "C" int qpdo_dev_residuals(qpdo_dev *d, int proximal, qpdo_dev_scalars *out)
 {
+    if (d) cudaSetDevice(d->device);
     {
         PhaseTimer t(d, PH_RES);
         ResArgs A;
@@ -517,6 +521,7 @@ extern "C" int qpdo_dev_residuals(qpdo_dev *d, int proximal, qpdo_dev_scalars *o
 
 extern "C" int qpdo_dev_newton_step(qpdo_dev *d, int force_reset, int proximal)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m;
     d->proximal = proximal;
     {
@@ -560,6 +565,7 @@ extern "C" int qpdo_dev_newton_step(qpdo_dev *d, int force_reset, int proximal)
 extern "C" int qpdo_dev_outer_update(qpdo_dev *d, int do_mu, int do_sigma, int proximal, double eps_abs, double theta,
                                      double delta, double mu_min, double sigma_upd, double sigma_min, double *sigma)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m;
     PhaseTimer t(d, PH_OTHER);
     k_copy2<<<cdiv(std::max(n, m), TPB), TPB, 0, d->st>>>(d->x, d->xbar, n, d->y, d->ybar, m);       // qpdo.c:396-397
@@ -584,6 +590,7 @@ extern "C" int qpdo_dev_outer_update(qpdo_dev *d, int do_mu, int do_sigma, int p
 
 extern "C" int qpdo_dev_primal_infeasible(qpdo_dev *d, double eps, int *flag)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m, scaled = d->scaling_iters > 0;
     *flag = 0;
     if (!m) return 0;
@@ -614,6 +621,7 @@ extern "C" int qpdo_dev_primal_infeasible(qpdo_dev *d, double eps, int *flag)
 
 extern "C" int qpdo_dev_dual_infeasible(qpdo_dev *d, double eps, int proximal, int *flag)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m, scaled = d->scaling_iters > 0;
     *flag = 0;
     PhaseTimer t(d, PH_OTHER);
@@ -650,6 +658,7 @@ extern "C" int qpdo_dev_dual_infeasible(qpdo_dev *d, double eps, int proximal, i
 extern "C" int qpdo_dev_store_solution(qpdo_dev *d, double *sol_x, double *sol_y, double *x, double *y, double *dx,
                                        double *dy, long *active_set, qpdo_dev_scalars *out)
 {
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, m = d->m;
     const size_t nb = sizeof(double) * n, mb = sizeof(double) * m;
     k_store_solution<<<cdiv(std::max(n, m), TPB), TPB, 0, d->st>>>(d->x, d->y, d->D, d->E, d->cinv, d->scaling_iters > 0,
@@ -672,6 +681,7 @@ extern "C" int qpdo_dev_store_solution(qpdo_dev *d, double *sol_x, double *sol_y
 
 extern "C" int qpdo_dev_update_bounds(qpdo_dev *d, const double *l, const double *u)
 {   // qpdo.c:538-543
+    if (d) cudaSetDevice(d->device);
     const int m = d->m, scaled = d->scaling_iters > 0;
     if (!m) return 0;
     if (l) {
@@ -700,6 +710,7 @@ __global__ void k_gather_vals(double *dst, const double *src, const int *idx, in
 extern "C" int qpdo_dev_update_q(qpdo_dev *d, const double *q, int proximal, double sigma_init, double *sigma,
                                  double *c, double *cinv, double *norm_q)
 {   // qpdo.c:549-586
+    if (d) cudaSetDevice(d->device);
     const int n = d->n, scaled = d->scaling_iters > 0;
     CUDA_OK(cudaMemcpyAsync(d->q, q, sizeof(double) * n, cudaMemcpyHostToDevice, d->st));
     if (scaled) {
@@ -736,6 +747,7 @@ extern "C" int qpdo_dev_update_q(qpdo_dev *d, const double *q, int proximal, dou
 
 extern "C" long qpdo_dev_get_vector(qpdo_dev *d, const char *name, double *out, long cap)
 {
+    if (d) cudaSetDevice(d->device);
     struct { const char *nm; const double *p; int len; } tab[] = {
         {"x", d->x, d->n}, {"y", d->y, d->m}, {"xbar", d->xbar, d->n}, {"ybar", d->ybar, d->m}, {"Ax", d->Ax_, d->m},
         {"Qx", d->Qx_, d->n}, {"Aty", d->Aty, d->n}, {"mu", d->mu, d->m}, {"sqrt_mu", d->sqrt_mu, d->m}, {"w", d->w, d->m},
@@ -759,6 +771,7 @@ extern "C" long qpdo_dev_get_vector(qpdo_dev *d, const char *name, double *out, 
 
 extern "C" int qpdo_dev_test_spmv(qpdo_dev *d, int which, const double *x, double *y)
 {
+    if (d) cudaSetDevice(d->device);
     const int nin = which == 1 ? d->m : d->n, nout = which == 0 ? d->m : d->n;
     double *din = which == 1 ? d->tmp_m : d->tmp_n, *dout = which == 0 ? d->Adx : d->Qdx;
     CUDA_OK(cudaMemcpyAsync(din, x, sizeof(double) * nin, cudaMemcpyHostToDevice, d->st));
@@ -772,6 +785,7 @@ extern "C" int qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const dou
                                         const double *y, const double *mu, const double *sqrt_mu, const double *Adx,
                                         const double *w, const double *l, const double *u, double *tau)
 {
+    if (d) cudaSetDevice(d->device);
     struct { double *dst; const double *src; int len; } up[] = {
         {d->dx, dx, d->n}, {d->Qdx, Qdx, d->n}, {d->df, df, d->n}, {d->dy, dy, d->m}, {d->y, y, d->m}, {d->mu, mu, d->m},
         {d->sqrt_mu, sqrt_mu, d->m}, {d->Adx, Adx, d->m}, {d->w, w, d->m}, {d->l, l, d->m}, {d->u, u, d->m}};
@@ -788,6 +802,7 @@ extern "C" int qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const dou
 extern "C" int qpdo_dev_test_factor_solve(qpdo_dev *d, const double *omega, double sigma, const double *b, double *x,
                                           float *factor_ms, float *solve_ms)
 {
+    if (d) cudaSetDevice(d->device);
     cudaEvent_t e0, e1, e2;
     cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
     if (d->m) CUDA_OK(cudaMemcpyAsync(d->omega, omega, sizeof(double) * d->m, cudaMemcpyHostToDevice, d->st));

@@ -404,11 +404,8 @@ __global__ void k_sweep_final(const double *cand, int nblk, const double *bs, co
 // =============================================================================== host side
 int linesearch_setup(qpdo_dev *d)
 {
-    static bool attr_done = false;
-    if (!attr_done) {
-        CUDA_OK(cudaFuncSetAttribute(k_sort_scan_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(unsigned) * 1024 * (SCAN_SMEM_MAX_PER | 1))));
-        attr_done = true;
-    }
+    // function attributes are per device: set for the device of every new context (no process-wide flag)
+    CUDA_OK(cudaFuncSetAttribute(k_sort_scan_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(unsigned) * 1024 * (SCAN_SMEM_MAX_PER | 1))));
     const size_t M2 = 2 * (size_t)d->m;
     d->sort_blocks = std::max(1, cdiv((long)M2, SORT_TILE));
     d->ls_blocks = std::max(1, std::min(592, cdiv(std::max(d->n, 2 * d->m), 256)));

@@ -246,3 +246,40 @@ def test_batch_solve_data_entry_with_reference_structs(oracle_mod):
         assert (int(summ[i]["status_val"]), int(summ[i]["iterations"])) == (o.status_val, o.iterations)
         assert rel_err(o.x, xs[i]) <= TOL and rel_err(o.y, ys[i]) <= TOL
         assert abs(float(summ[i]["objective"]) - o.objective) <= TOL * max(1.0, abs(o.objective))
+
+
+@pytest.mark.gpu
+def test_batch_adaptive_order_and_bad_bounds_and_multi():
+    """queue order (longest first, from the previous solve) must not change a single bit of the results; an instance
+    with l > u is reported as QPDO_ERROR (validate_data, src/validate.c:19-28) without touching its neighbours;
+    qpdo_batch_solve_multi over however many GPUs the box has gives the same bytes as one batch."""
+    B = 1500
+    b = problems.mpc_batch(B, first=3000)
+    bt, vals = qbatch.from_mpc(b)
+    ref = bt.solve(*vals)
+    bt.set_adaptive_order(True)
+    a1 = bt.solve(*vals)           # natural order, leaves the order behind
+    a2 = bt.solve(*vals)           # longest first
+    for r in (a1, a2):
+        assert all(np.array_equal(u, v) for u, v in zip(ref, r))
+    bt.set_adaptive_order(False)
+    Qx, Ax, q, l, u = [v.copy() for v in vals]
+    l[7, 3] = u[7, 3] + 1.0
+    x, y, s, act = bt.solve(Qx, Ax, q, l, u)
+    assert int(s[7]["status_val"]) == capi.QPDO_ERROR and int(s[7]["iterations"]) == 0
+    keep = np.arange(B) != 7
+    assert np.array_equal(s[keep], ref[2][keep]) and np.array_equal(x[keep], ref[0][keep])
+    bt.destroy()
+    import qpdo_b200
+    ng = qpdo_b200.lib().qpdo_dev_count()
+    bts = [qbatch.from_mpc(b, capacity=(B + ng - 1) // ng, device=g)[0] for g in range(ng)]
+    m = qbatch.solve_multi(bts, *vals)
+    for t in bts:
+        t.destroy()
+    assert all(np.array_equal(u, v) for u, v in zip(ref, m))
+    with pytest.raises(RuntimeError):
+        bt2, _ = qbatch.from_mpc(b, capacity=10)
+        try:
+            bt2.solve(*vals)        # count > capacity
+        finally:
+            bt2.destroy()
