@@ -397,6 +397,7 @@ template <int W> __device__ __forceinline__ void b_panel_update(const unsigned (
 #pragma unroll
     for (int e = 0; e < SN_EPTS; e++) b_sts_if(ea[e], av[e], pl[e] > thr);
 }
+#ifdef B_EXACT_PIVOTS
 // columns k0 .. k0 + W - 1 of the front (W <= nc - k0), executed by warp 0
 template <int W> __device__ __forceinline__ void b_panel_factor(double *L, double *xs, double *ucol, int f, int N, int base, int k0)
 {
@@ -447,6 +448,80 @@ template <int W> __device__ __forceinline__ void b_panel_factor(double *L, doubl
         for (int c = 0; c < W; c++) { us[2 * c * SN_W] = u[c]; us[(2 * c + 1) * SN_W] = l[c]; }
     }
 }
+#else
+// Fast pivots (default): the chain per pivot PAIR is fma -> reciprocal -> product instead of (reciprocal -> quotient
+// -> fma) twice.  With the 2 x 2 leading block [d0 u; u a] the second pivot is d1 = (d0 a - u^2) / d0, so
+// 1/d1 = d0 / (d0 a - u^2): both reciprocals start from loaded values and run side by side (the formula of a 2 x 2
+// block pivot; the cancellation in d0 a - u^2 is the one in a - u^2/d0 scaled by d0).  Multipliers are l = u * (1/d)
+// with a reciprocal accurate to an ulp (seed + two Newton steps) instead of the correctly rounded quotient: the
+// factorization is as backward stable as before, but no longer bit-identical to the column path (-DB_EXACT_PIVOTS
+// restores that variant; tools/batch_ab.py checks whichever is built).
+__device__ __forceinline__ double b_rcp2(double d)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0); r = fma(r, e, r);
+    e = fma(-d, r, 1.0); r = fma(r, e, r);
+    return r;
+}
+template <int W> __device__ __forceinline__ void b_panel_factor(double *L, double *xs, double *ucol, int f, int N, int base, int k0)
+{
+    const int t = threadIdx.x, rows = N - k0;                   // lane t: front row k0 + t; t == rows: the right-hand side
+    const int tc = t < rows ? t : rows;                           // lanes past the right-hand side repeat its work and store nothing
+    const bool live = t <= rows;
+    double *cq[W], *pa[W];                                        // column k0 + q, + front row;  this lane's entry of it
+    cq[0] = L + sn_col(base, k0, N);
+#pragma unroll
+    for (int q = 1; q < W; q++) cq[q] = cq[q - 1] + (N - k0 - q);
+#pragma unroll
+    for (int q = 0; q < W; q++) pa[q] = tc < rows ? cq[q] + k0 + tc : xs + f + k0 + q;
+    double a[W], B[W][W];
+#pragma unroll
+    for (int q = 0; q < W; q++) {
+#pragma unroll
+        for (int p = q; p < W; p++) B[p][q] = cq[q][k0 + p];
+        a[q] = *pa[q];                                            // lanes t < q read an unrelated entry: never used
+    }
+    double d[W], r[W], u[W], l[W];
+    if constexpr (W == 1) {
+        d[0] = B[0][0]; r[0] = b_rcp2(d[0]);
+        u[0] = a[0]; l[0] = u[0] * r[0];
+    } else {
+        // pivots 0, 1
+        const double det = fma(B[0][0], B[1][1], -(B[1][0] * B[1][0]));
+        r[0] = b_rcp2(B[0][0]);
+        const double rdet = b_rcp2(det);
+        d[0] = B[0][0]; d[1] = det * r[0]; r[1] = B[0][0] * rdet;
+        const double l10 = B[1][0] * r[0];
+        u[0] = a[0]; l[0] = u[0] * r[0];
+        u[1] = fma(-u[0], l10, a[1]); l[1] = u[1] * r[1];
+        if constexpr (W == 4) {
+            const double l20 = B[2][0] * r[0], l30 = B[3][0] * r[0];
+            const double u21 = fma(-B[2][0], l10, B[2][1]), u31 = fma(-B[3][0], l10, B[3][1]);
+            const double l21 = u21 * r[1], l31 = u31 * r[1];
+            const double s22 = fma(-u21, l21, fma(-B[2][0], l20, B[2][2]));
+            const double s32 = fma(-u31, l21, fma(-B[3][0], l20, B[3][2]));
+            const double s33 = fma(-u31, l31, fma(-B[3][0], l30, B[3][3]));
+            const double det2 = fma(s22, s33, -(s32 * s32));
+            r[2] = b_rcp2(s22);
+            const double rdet2 = b_rcp2(det2);
+            d[2] = s22; d[3] = det2 * r[2]; r[3] = s22 * rdet2;
+            const double l32 = s32 * r[2];
+            u[2] = fma(-u[1], l21, fma(-u[0], l20, a[2])); l[2] = u[2] * r[2];
+            u[3] = fma(-u[2], l32, fma(-u[1], l31, fma(-u[0], l30, a[3]))); l[3] = u[3] * r[3];
+        }
+    }
+    __syncwarp();                                                 // every lane has read the block before it is overwritten
+#pragma unroll
+    for (int c = 0; c < W; c++)
+        if (live && t >= c) *pa[c] = t == c ? d[c] : l[c];
+    if (live && t >= W) {
+        double *us = ucol + k0 + t;
+#pragma unroll
+        for (int c = 0; c < W; c++) { us[2 * c * SN_W] = u[c]; us[(2 * c + 1) * SN_W] = l[c]; }
+    }
+}
+#endif
 __device__ __forceinline__ void b_factor_front_small(const BatchPlan &P, double *L, double *xs, double *ucol, const int4 d0, const int4 d1)
 {
     const int tid = threadIdx.x;
