@@ -23,6 +23,7 @@
 #include <vector>
 
 #define BNT 128                 // threads per CTA
+#define B_ORDER_BINS 4096        // adaptive queue order: iteration counts are binned up to this value
 #define BNW (BNT / 32)
 #ifndef B_MINCTAS
 #define B_MINCTAS 4              // resident CTAs per SM the register budget is sized for
@@ -102,6 +103,8 @@ struct BatchIO {
     int count;
     int *next;                               // work queue head
     const int *order;                        // the k-th pull of the queue takes instance order[k] (null: k itself)
+    int *order_out;                          // adaptive order: the last CTA to finish leaves the order of the NEXT solve here (or null)
+    int *done;                               // CTAs that have left the queue loop
     long long *timing;                       // [count][8] clock64 cycles per phase (diagnostics) or NULL
 };
 
@@ -1318,28 +1321,40 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC Batch
         const int b = io.order ? io.order[s_b] : s_b;
         b_solve_instance(P, io, V, b);
     }
-}
-
-// Queue order for the NEXT solve of the same instances: longest first, by the iteration counts of the solve that
-// just finished (counting sort, one CTA; ties in arbitrary order -- the order only schedules, results do not depend
-// on it).  A receding-horizon loop re-solves similar problems, and the ragged tail of a launch is set by where the
-// longest instances start.
-#define B_ORDER_BINS 4096
-__global__ void __launch_bounds__(1024) k_batch_order(const qpdo_batch_summary *summary, int count, int *order)
-{
-    __shared__ int bins[B_ORDER_BINS];
-    for (int t = threadIdx.x; t < B_ORDER_BINS; t += blockDim.x) bins[t] = 0;
-    __syncthreads();
-    for (int i = threadIdx.x; i < count; i += blockDim.x) {
-        int it = summary[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
-        atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1);                 // descending
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) { int acc = 0; for (int t = 0; t < B_ORDER_BINS; t++) { const int c = bins[t]; bins[t] = acc; acc += c; } }
-    __syncthreads();
-    for (int i = threadIdx.x; i < count; i += blockDim.x) {
-        int it = summary[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
-        order[atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1)] = i;
+    // Queue order for the NEXT solve of the same instances: longest first, by the iteration counts this launch has
+    // just produced (counting sort; ties in arbitrary order -- the order only schedules, results do not depend on it).
+    // A receding-horizon loop re-solves similar problems, and the ragged tail of a launch is set by where the longest
+    // instances start.  Done by the last CTA to leave the queue (a separate kernel could not become resident beside
+    // the persistent CTAs of the other stream's launch: they hold every register of the SM).
+    if (io.order_out) {
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_b = atomicAdd(io.done, 1);
+        __syncthreads();
+        if (s_b == (int)gridDim.x - 1) {
+            __threadfence();
+            int *bins = (int *)sm;                                   // B_ORDER_BINS counters, then the scan partials
+            for (int t = threadIdx.x; t < B_ORDER_BINS + BNT; t += BNT) bins[t] = 0;
+            __syncthreads();
+            for (int i = threadIdx.x; i < io.count; i += BNT) {
+                int it = ((volatile const qpdo_batch_summary *)io.summary)[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
+                atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1);          // descending
+            }
+            __syncthreads();
+            const int per = B_ORDER_BINS / BNT, t0 = threadIdx.x * per;
+            int acc = 0;
+            for (int t = 0; t < per; t++) acc += bins[t0 + t];
+            bins[B_ORDER_BINS + threadIdx.x] = acc;
+            __syncthreads();
+            int off = 0;
+            for (int w = 0; w < (int)threadIdx.x; w++) off += bins[B_ORDER_BINS + w];
+            for (int t = 0; t < per; t++) { const int c = bins[t0 + t]; bins[t0 + t] = off; off += c; }
+            __syncthreads();
+            for (int i = threadIdx.x; i < io.count; i += BNT) {
+                int it = ((volatile const qpdo_batch_summary *)io.summary)[i].iterations; it = it < 0 ? 0 : it >= B_ORDER_BINS ? B_ORDER_BINS - 1 : it;
+                io.order_out[atomicAdd(&bins[B_ORDER_BINS - 1 - it], 1)] = i;
+            }
+        }
     }
 }
 
@@ -1627,6 +1642,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.rho = s->rho; P.theta = s->theta; P.delta = s->delta; P.mu_min = s->mu_min; P.sigma_init = s->sigma_init;
         P.sigma_upd = s->sigma_upd; P.sigma_min = s->sigma_min;
         b->smem = sizeof(double) * ((size_t)nnzA + nnzQ + 12 * (size_t)n + 16 * (size_t)m + P.karea + BNW * 8 + 2 * SN_PW * (size_t)P.ucolw) + 2 * (size_t)m + 16;
+        b->smem = std::max(b->smem, sizeof(int) * (size_t)(B_ORDER_BINS + BNT));
         if (b->smem > 227 * 1024) {
             qpdo_set_error("qpdo_batch_create: a problem of this size needs %zu bytes of shared memory per CTA (limit 232448): use qpdo_setup/qpdo_solve", b->smem);
             break;
@@ -1643,7 +1659,7 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         if (b_alloc(b, &b->dQx, cap * nnzQ) || b_alloc(b, &b->dAx, cap * nnzA) || b_alloc(b, &b->dq, cap * n) || b_alloc(b, &b->dl, cap * m) ||
             b_alloc(b, &b->du, cap * m) || b_alloc(b, &b->dc, cap) || b_alloc(b, &b->dx0, cap * n) || b_alloc(b, &b->dy0, cap * m) ||
             b_alloc(b, &b->dx, cap * n) || b_alloc(b, &b->dy, cap * m) || b_alloc(b, &b->dsum, cap) || b_alloc(b, &b->dact, cap * m) ||
-            b_alloc(b, &b->next, 2) || b_alloc(b, &b->dorder, cap))
+            b_alloc(b, &b->next, 4) || b_alloc(b, &b->dorder, cap))
             break;
         rc = 0;
     } while (0);
@@ -1665,13 +1681,12 @@ static int batch_launch(qpdo_batch *b, cudaStream_t st, int *next, int first, in
     io.active = dactive ? dactive + o * m : nullptr; io.count = count; io.next = next;
     io.timing = b->timing ? b->timing + o * 8 : nullptr;
     io.order = use_order ? b->dorder + o : nullptr;
+    io.order_out = (b->adaptive && dsummary) ? b->dorder + o : nullptr;
+    io.done = next + 2;                                                // next[0..1]: queue heads of the two streams, next[2..3]: their exit counters
     CUDA_OK(cudaMemsetAsync(next, 0, sizeof(int), st));
+    CUDA_OK(cudaMemsetAsync(next + 2, 0, sizeof(int), st));
     k_batch_solve<<<std::min(count, b->ctas), BNT, b->smem, st>>>(b->P, io);
     CUDA_OK(cudaGetLastError());
-    if (b->adaptive && dsummary) {
-        k_batch_order<<<1, 1024, 0, st>>>(dsummary + o, count, b->dorder + o);
-        CUDA_OK(cudaGetLastError());
-    }
     return 0;
 }
 
@@ -1701,6 +1716,8 @@ extern "C" int qpdo_batch_solve_device(qpdo_batch *b, int count, const double *d
 // small part of the call, few enough that every chunk still fills the resident CTAs several times over
 static int batch_chunks(const qpdo_batch *b, int count)
 {
+    static const int forced = getenv("QPDO_BATCH_CHUNKS") ? atoi(getenv("QPDO_BATCH_CHUNKS")) : 0;                 // experiments
+    if (forced > 0) return forced;
     int nchunk = count / (3 * b->ctas);
     return nchunk < 1 ? 1 : nchunk > 8 ? 8 : nchunk;
 }
@@ -1717,7 +1734,8 @@ static int batch_solve_issue(qpdo_batch *b, int count, const double *Qx, const d
     // chunk k-1 overlap the kernel of chunk k (with pinned host buffers; pageable ones just serialise), and the
     // ragged tail of one chunk's launch is filled by the head of the next
     const int nchunk = batch_chunks(b, count);
-    const bool use_order = b->adaptive && b->order_count == count && b->order_chunks == nchunk;
+    static const int host_order = getenv("QPDO_BATCH_HOST_ORDER") ? atoi(getenv("QPDO_BATCH_HOST_ORDER")) : 1;     // experiments
+    const bool use_order = host_order && b->adaptive && b->order_count == count && b->order_chunks == nchunk;
     for (int k = 0; k < nchunk; k++) {
         const int lo = (int)((long)count * k / nchunk), hi = (int)((long)count * (k + 1) / nchunk), cn = hi - lo;
         if (cn <= 0) continue;
