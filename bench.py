@@ -493,6 +493,8 @@ def run_c1(args, dist):
     s.warm_start(None, None); s.solve()
     lib.qpdo_dev_get_profile(s.device, C.byref(prof), 1)
     lib.qpdo_dev_set_profiling(s.device, 0)           # the phase timers synchronise: the timed steps run without them
+    sinfo = capi.DevSymbolicInfo()
+    lib.qpdo_dev_get_symbolic_info(s.device, C.byref(sinfo))
     dist.barrier()
     ts = []
     with ClockSampler(dist.local) as clk:
@@ -516,6 +518,10 @@ def run_c1(args, dist):
             "best_ms": float(np.min(ts)) * 1e3,
             "kkt_ms_per_newton": (prof.assemble_ms + prof.factor_ms + prof.solve_ms) / newton,
             "launches_per_newton_step": prof.kernel_launches / float(newton), "newton_steps": int(prof.n_newton),
+            "phases_ms_per_newton": {"assemble": prof.assemble_ms / newton, "factor": prof.factor_ms / newton, "solve": prof.solve_ms / newton,
+                                     "spmv": prof.spmv_ms / newton, "linesearch": prof.linesearch_ms / newton,
+                                     "residual": prof.residual_ms / max(1, prof.n_residual), "other": prof.other_ms / newton},
+            "symbolic": {"nsuper": sinfo.nsuper, "nlevel": sinfo.nlevel, "max_front": sinfo.max_front, "lnz": int(sinfo.lnz), "flops": sinfo.flops},
             "result": {"status": r.status_val, "iterations": r.iterations, "oterations": r.oterations, "objective": r.objective},
             "roofline": {"bound": "latency", "kernel": "whole loop pass (launch / dependency latency; HBM and FP64 pipes idle at n=1000)",
                          "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None},
