@@ -194,3 +194,164 @@ extern "C" int qpdo_order_mindeg(int n, const int64_t *gp, const int *gi, int *p
     }
     return k == n ? 0 : -1;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Nested dissection by level structures (George's automatic nested dissection) with minimum-degree
+// leaves.  A PDE-type graph (CONT-300: a 13-point stencil on a 300 x 300 grid) under minimum degree
+// alone ends in a tall, thin top of the assembly tree -- one big front after another, i.e. one serial
+// chain of 32-pivot panel steps on the GPU.  Dissection gives the top a logarithmic height and several
+// fronts per level.  Separator of a connected piece = one BFS level from a pseudo-peripheral vertex
+// (edges only join equal or adjacent levels), chosen among the levels that split the piece 35/65 or
+// better for the fewest vertices, then thinned (vertices without a neighbour in the next level move to
+// the first part).  Pieces of at most `leaf` vertices, and pieces whose level structure is too shallow
+// to cut (random graphs), are ordered by minimum degree on the induced subgraph.
+namespace {
+
+struct NDWork {
+    int n;
+    const int64_t *gp;
+    const int *gi;
+    std::vector<int> piece;      // piece id of every vertex (only vertices of the current piece carry its id)
+    std::vector<int> level;      // BFS level, valid when lstamp[v] == stamp
+    std::vector<int> lstamp;
+    std::vector<int> local;      // global -> local index inside a leaf
+    int stamp = 0;
+    std::vector<int> order;      // elimination order being built (separators are placed by the recursion)
+};
+
+// BFS over the vertices with piece[v] == id from `root`; returns the vertices in visiting order, `ends` = level starts
+static void nd_bfs(NDWork &W, int id, int root, std::vector<int> &out, std::vector<int> &ends)
+{
+    out.clear(); ends.clear();
+    W.stamp++;
+    W.lstamp[root] = W.stamp; W.level[root] = 0;
+    out.push_back(root);
+    size_t head = 0;
+    int cur = 0;
+    ends.push_back(0);
+    while (head < out.size()) {
+        const int v = out[head++];
+        if (W.level[v] != cur) { cur = W.level[v]; ends.push_back((int)head - 1); }
+        for (int64_t t = W.gp[v]; t < W.gp[v + 1]; t++) {
+            const int u = W.gi[t];
+            if (W.piece[u] != id || W.lstamp[u] == W.stamp) continue;
+            W.lstamp[u] = W.stamp; W.level[u] = W.level[v] + 1;
+            out.push_back(u);
+        }
+    }
+    ends.push_back((int)out.size());
+}
+
+static void nd_leaf(NDWork &W, const std::vector<int> &verts, int id)
+{
+    const int k = (int)verts.size();
+    if (k <= 2) { for (int v : verts) W.order.push_back(v); return; }
+    for (int i = 0; i < k; i++) W.local[verts[i]] = i;
+    std::vector<int64_t> lp(k + 1, 0);
+    std::vector<int> li;
+    for (int i = 0; i < k; i++) {
+        const int v = verts[i];
+        for (int64_t t = W.gp[v]; t < W.gp[v + 1]; t++) if (W.piece[W.gi[t]] == id) li.push_back(W.local[W.gi[t]]);
+        lp[i + 1] = (int64_t)li.size();
+    }
+    std::vector<int> lperm(k);
+    if (li.empty() || qpdo_order_mindeg(k, lp.data(), li.data(), lperm.data()) != 0) { for (int v : verts) W.order.push_back(v); return; }
+    for (int i = 0; i < k; i++) W.order.push_back(verts[lperm[i]]);
+}
+
+} // namespace
+
+extern "C" int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_out, int leaf)
+{
+    if (n <= 0) return 0;
+    if (leaf < 8) leaf = 8;
+    NDWork W;
+    W.n = n; W.gp = gp; W.gi = gi;
+    W.piece.assign(n, 0); W.level.assign(n, 0); W.lstamp.assign(n, 0); W.local.assign(n, 0);
+    W.order.reserve(n);
+    // explicit stack of tasks: {piece id, kind}; kind 0 = dissect the piece, kind 1 = emit a stored separator
+    struct Task { int id; int kind; };
+    std::vector<Task> stack;
+    std::vector<std::vector<int>> verts(1), seps(1);        // per piece id: its vertices / its separator
+    verts[0].resize(n);
+    for (int v = 0; v < n; v++) verts[0][v] = v;
+    stack.push_back({0, 0});
+    std::vector<int> bfs, ends, bfs2, ends2;
+    while (!stack.empty()) {
+        const Task tk = stack.back(); stack.pop_back();
+        if (tk.kind == 1) { nd_leaf(W, seps[tk.id], -1 - tk.id); std::vector<int>().swap(seps[tk.id]); continue; }
+        const int id = tk.id;
+        std::vector<int> V; V.swap(verts[id]);
+        const int k = (int)V.size();
+        if (k == 0) continue;
+        if (k <= leaf) { nd_leaf(W, V, id); continue; }
+        // connected components of the piece in one sweep (a pattern with few active rows is mostly isolated
+        // vertices): small components go straight to the order, the others become pieces of their own
+        nd_bfs(W, id, V[0], bfs, ends);
+        if ((int)bfs.size() < k) {
+            std::vector<int> todo;                          // new piece ids, dissected in discovery order
+            size_t vi = 0;
+            std::vector<int> comp; comp.swap(bfs);
+            for (;;) {
+                if ((int)comp.size() <= leaf && comp.size() <= 2) { for (int v : comp) { W.piece[v] = -2000000000; W.order.push_back(v); } }
+                else {
+                    const int idc = (int)verts.size();
+                    verts.emplace_back(comp); seps.emplace_back();
+                    for (int v : comp) W.piece[v] = idc;
+                    todo.push_back(idc);
+                }
+                while (vi < V.size() && W.piece[V[vi]] != id) vi++;
+                if (vi >= V.size()) break;
+                nd_bfs(W, id, V[vi], comp, ends);
+            }
+            for (size_t t = todo.size(); t-- > 0;) stack.push_back({todo[t], 0});
+            continue;
+        }
+        // pseudo-peripheral root: restart from a minimum-degree vertex of the last level while the depth grows
+        int root = V[0], depth = (int)ends.size() - 1;
+        for (int it = 0; it < 4; it++) {
+            const int lb = ends[ends.size() - 2], le = ends[ends.size() - 1];
+            int best = bfs[lb]; int64_t bd = gp[best + 1] - gp[best];
+            for (int t = lb; t < le; t++) { const int64_t dgr = gp[bfs[t] + 1] - gp[bfs[t]]; if (dgr < bd) { bd = dgr; best = bfs[t]; } }
+            nd_bfs(W, id, best, bfs2, ends2);
+            const int d2 = (int)ends2.size() - 1;
+            if (d2 > depth) { depth = d2; root = best; bfs.swap(bfs2); ends.swap(ends2); } else break;
+        }
+        (void)root;
+        const int nlev = (int)ends.size() - 1;
+        if (nlev < 5) { nd_leaf(W, V, id); continue; }    // too shallow to cut (dense / random graph): minimum degree
+        // separator level: among levels leaving >= 35 % on both sides the one with the fewest vertices
+        int bestl = -1, bests = k + 1;
+        for (int l = 1; l + 1 < nlev; l++) {
+            const int before = ends[l], after = k - ends[l + 1], sz = ends[l + 1] - ends[l];
+            if (before * 100 >= 35 * k && after * 100 >= 35 * k && sz < bests) { bests = sz; bestl = l; }
+        }
+        if (bestl < 0) {                                   // no balanced level: the one nearest the middle
+            int bestd = k + 1;
+            for (int l = 1; l + 1 < nlev; l++) { const int dlt = abs(ends[l] - (k - ends[l + 1])); if (dlt < bestd) { bestd = dlt; bestl = l; } }
+        }
+        if (bestl < 0) { nd_leaf(W, V, id); continue; }
+        const int ida = (int)verts.size(), idb = ida + 1;
+        verts.emplace_back(); verts.emplace_back(); seps.emplace_back(); seps.emplace_back();
+        // levels carry the stamp of the BFS that is in `bfs` now: re-run it if the last probe did not win
+        nd_bfs(W, id, bfs[0], bfs, ends);
+        for (int t = 0; t < k; t++) {
+            const int v = bfs[t], l = W.level[v];
+            if (l < bestl) { W.piece[v] = ida; verts[ida].push_back(v); }
+            else if (l > bestl) { W.piece[v] = idb; verts[idb].push_back(v); }
+        }
+        for (int t = ends[bestl]; t < ends[bestl + 1]; t++) {
+            const int v = bfs[t];
+            bool touches = false;
+            for (int64_t e = gp[v]; e < gp[v + 1] && !touches; e++) touches = (W.piece[gi[e]] == idb);
+            if (touches) { W.piece[v] = -1 - id; seps[id].push_back(v); }
+            else { W.piece[v] = ida; verts[ida].push_back(v); }
+        }
+        stack.push_back({id, 1});          // emitted after both parts
+        stack.push_back({idb, 0});
+        stack.push_back({ida, 0});
+    }
+    if ((int)W.order.size() != n) return -1;
+    for (int i = 0; i < n; i++) perm_out[i] = W.order[i];
+    return 0;
+}

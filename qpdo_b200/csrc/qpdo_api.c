@@ -231,7 +231,7 @@ QPDOWorkspace *qpdo_setup(const QPDOData *data, const QPDOSettings *settings)
     qpdo_dev_problem P;
     qpdo_dev *dev = NULL;
     const char *ord_env;
-    int ordering = 1;
+    int ordering = 2;           /* nested dissection with minimum-degree leaves (falls back to minimum degree on graphs too shallow to cut) */
 
     if (!validate_data(data)) { eprint("Data validation returned failure"); return QPDO_NULL; }
     if (!validate_settings(settings)) { eprint("Settings validation returned failure"); return QPDO_NULL; }
@@ -265,6 +265,8 @@ QPDOWorkspace *qpdo_setup(const QPDOData *data, const QPDOSettings *settings)
     P.q = data->q; P.l = data->l; P.u = data->u;
     ord_env = getenv("QPDO_B200_ORDERING");
     if (ord_env && !strcmp(ord_env, "natural")) ordering = 0;
+    if (ord_env && !strcmp(ord_env, "mindeg")) ordering = 1;
+    if (ord_env && !strcmp(ord_env, "nd")) ordering = 2;
     if (qpdo_dev_create(&dev, &P, (int)settings->scaling, ordering, -1)) {
         eprint("CUDA layer: %s", qpdo_dev_last_error());
         goto fail;

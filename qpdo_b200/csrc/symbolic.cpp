@@ -83,6 +83,13 @@ extern "C" qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, con
     // ------------------------------------------------------------------ ordering
     std::vector<int> perm(n), pinv(n);
     if (ordering == 0) std::iota(perm.begin(), perm.end(), 0);
+    else if (ordering == 2) {
+        const char *lf = getenv("QPDO_ND_LEAF");
+        if (qpdo_order_nd(n, gp.data(), gi.data(), perm.data(), lf ? atoi(lf) : 256) != 0) {
+            if (err) snprintf(err, 256, "nested-dissection ordering failed");
+            return NULL;
+        }
+    }
     else if (qpdo_order_mindeg(n, gp.data(), gi.data(), perm.data()) != 0) {
         if (err) snprintf(err, 256, "minimum-degree ordering failed");
         return NULL;

@@ -59,7 +59,7 @@ typedef struct qpdo_symbolic {
 } qpdo_symbolic;
 
 /* Inputs are clean int32 CSC with sorted, duplicate-free row indices: Q lower triangle (n x n),
- * A (m x n).  ordering: 0 = natural, 1 = minimum degree (default).  Returns NULL on failure and
+ * A (m x n).  ordering: 0 = natural, 1 = minimum degree (default), 2 = nested dissection (level structures, minimum-degree leaves).  Returns NULL on failure and
  * writes a message into err (if non-NULL, at least 256 bytes). */
 qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, const int *Qi,
                                      const int *Ap, const int *Ai, int ordering, char *err);
@@ -68,6 +68,8 @@ void qpdo_symbolic_free(qpdo_symbolic *S);
 /* fill-reducing ordering alone (exposed for tests): graph in CSC-like adjacency form without
  * self loops, symmetric; perm_out[new] = old */
 int qpdo_order_mindeg(int n, const int64_t *gp, const int *gi, int *perm_out);
+/* nested dissection by BFS level structures with minimum-degree leaves of at most `leaf` vertices */
+int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_out, int leaf);
 
 #ifdef __cplusplus
 }
