@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <stdlib.h>
 #include <string.h>
+#include <type_traits>
 #include <vector>
 
 #define BNT 128                 // threads per CTA
@@ -88,6 +89,7 @@ struct BatchPlan {
     const int *Sptr, *Srow;                  // rows below the pivot block (permuted indices)
     const int *Uptr, *Upos;                  // where the (row ib, col jb) update entry lives in the ancestors' trapezoids
     int max_front, ucolw, nSrow;
+    int ls_sep;                              // linesearch scratch lives outside the L area (L survives the step: unchanged K is not refactored)
     const int2 *Emap2;                       // owned entries of each front: {i | j << 8, position in L or ~index into xs}, column major, j >= 1, i = j..N
     const int4 *sn_desc;                     // per supernode {f, nc, nr, base}, {Sptr, Eptr, ne, 0}
     // settings (reference include/types.h:96-116)
@@ -485,16 +487,16 @@ template <int W> __device__ __forceinline__ void b_panel_factor(double *L, doubl
         for (int p = q; p < W; p++) B[p][q] = cq[q][k0 + p];
         a[q] = *pa[q];                                            // lanes t < q read an unrelated entry: never used
     }
-    double d[W], r[W], u[W], l[W];
+    double r[W], u[W], l[W];
     if constexpr (W == 1) {
-        d[0] = B[0][0]; r[0] = b_rcp2(d[0]);
+        r[0] = b_rcp2(B[0][0]);
         u[0] = a[0]; l[0] = u[0] * r[0];
     } else {
         // pivots 0, 1
         const double det = fma(B[0][0], B[1][1], -(B[1][0] * B[1][0]));
         r[0] = b_rcp2(B[0][0]);
         const double rdet = b_rcp2(det);
-        d[0] = B[0][0]; d[1] = det * r[0]; r[1] = B[0][0] * rdet;
+        r[1] = B[0][0] * rdet;
         const double l10 = B[1][0] * r[0];
         u[0] = a[0]; l[0] = u[0] * r[0];
         u[1] = fma(-u[0], l10, a[1]); l[1] = u[1] * r[1];
@@ -508,7 +510,7 @@ template <int W> __device__ __forceinline__ void b_panel_factor(double *L, doubl
             const double det2 = fma(s22, s33, -(s32 * s32));
             r[2] = b_rcp2(s22);
             const double rdet2 = b_rcp2(det2);
-            d[2] = s22; d[3] = det2 * r[2]; r[3] = s22 * rdet2;
+            r[3] = s22 * rdet2;
             const double l32 = s32 * r[2];
             u[2] = fma(-u[1], l21, fma(-u[0], l20, a[2])); l[2] = u[2] * r[2];
             u[3] = fma(-u[2], l32, fma(-u[1], l31, fma(-u[0], l30, a[3]))); l[3] = u[3] * r[3];
@@ -517,7 +519,7 @@ template <int W> __device__ __forceinline__ void b_panel_factor(double *L, doubl
     __syncwarp();                                                 // every lane has read the block before it is overwritten
 #pragma unroll
     for (int c = 0; c < W; c++)
-        if (live && t >= c) *pa[c] = t == c ? d[c] : l[c];
+        if (live && t >= c) *pa[c] = t == c ? r[c] : l[c];        // the diagonal keeps 1 / d_c: what the forward solve of an unchanged K multiplies by
     if (live && t >= W) {
         double *us = ucol + k0 + t;
 #pragma unroll
@@ -715,6 +717,55 @@ __device__ B_FN void b_backward_sn(const BatchPlan &P, const double *L, double *
     }
 }
 
+#ifndef B_EXACT_PIVOTS
+// z = D^{-1} L^{-1} xs on a factor that is already in place (K unchanged since the last factorization: the reference
+// keeps its factor too when no constraint enters or leaves, src/newton.c:24-33).  Lane t owns front row t; four pivot
+// columns per step: every lane fetches the four right-hand-side values (shuffles) and the six L entries between those
+// rows (broadcast loads), forms u_0..u_3 redundantly and applies them to its own row.  Per entry the fma sequence of
+// the fused forward solve of b_factor_front_small (ascending pivot, fma(-u_c, l_jc, .)), then u_c times the stored
+// reciprocal: bit-identical to factoring again.
+__device__ B_FN void b_forward_sn(const BatchPlan &P, const double *L, double *xs)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned Ls = b_saddr(L);
+    for (int s = 0; s < P.nsuper; s++) {
+        const int4 d0 = s_desc[2 * s], d1 = s_desc[2 * s + 1];
+        const int f = d0.x, nc = d0.y, nr = d0.z, N = nc + nr, base = d0.w;
+        const int tl = lane < N ? lane : N - 1;                        // lanes past the front repeat its last row and store nothing
+        const int xi = tl < nc ? f + tl : s_rows[d1.x + tl - nc];
+        double b = xs[xi];
+        // a0 = &L(row tl, column c0) as a shared-space byte address; column c+1 starts N - c - 1 entries after column c
+        unsigned a0 = Ls + 8u * (unsigned)(sn_col(base, 0, N) + tl);
+        unsigned g0 = Ls + 8u * (unsigned)sn_col(base, 0, N);          // &L(row 0, column c0) - 8 * 0: block entries are at + 8 * row
+        int stepc = N - 1;                                             // distance from column c0 to c0 + 1
+#pragma unroll 1
+        for (int c0 = 0; c0 < nc; c0 += 4) {
+            const unsigned a1 = a0 + 8u * (unsigned)stepc, a2 = a1 + 8u * (unsigned)(stepc - 1), a3 = a2 + 8u * (unsigned)(stepc - 2);
+            const unsigned g1 = g0 + 8u * (unsigned)stepc, g2 = g1 + 8u * (unsigned)(stepc - 1);
+            const unsigned r0 = 8u * (unsigned)c0;
+            const double l10 = b_lds<8>(g0 + r0), l20 = b_lds<16>(g0 + r0), l30 = b_lds<24>(g0 + r0);
+            const double l21 = b_lds<16>(g1 + r0), l31 = b_lds<24>(g1 + r0), l32 = b_lds<24>(g2 + r0);
+            double m0 = b_lds<0>(a0), m1 = b_lds<0>(a1), m2 = b_lds<0>(a2), m3 = b_lds<0>(a3);
+            m0 = tl > c0 ? m0 : 0.0; m1 = (tl > c0 + 1 && c0 + 1 < nc) ? m1 : 0.0;
+            m2 = (tl > c0 + 2 && c0 + 2 < nc) ? m2 : 0.0; m3 = (tl > c0 + 3 && c0 + 3 < nc) ? m3 : 0.0;
+            const double u0 = __shfl_sync(0xffffffffu, b, c0), v1 = __shfl_sync(0xffffffffu, b, c0 + 1);
+            const double v2 = __shfl_sync(0xffffffffu, b, c0 + 2), v3 = __shfl_sync(0xffffffffu, b, c0 + 3);
+            double u1 = fma(-u0, l10, v1);
+            double u2 = fma(-u1, l21, fma(-u0, l20, v2));
+            double u3 = fma(-u2, l32, fma(-u1, l31, fma(-u0, l30, v3)));
+            u1 = c0 + 1 < nc ? u1 : 0.0; u2 = c0 + 2 < nc ? u2 : 0.0; u3 = c0 + 3 < nc ? u3 : 0.0;     // columns past the pivot block do not exist
+            b = fma(-u0, m0, b); b = fma(-u1, m1, b); b = fma(-u2, m2, b); b = fma(-u3, m3, b);
+            a0 = a3 + 8u * (unsigned)(stepc - 3); g0 = g2 + 8u * (unsigned)(stepc - 2) + 8u * (unsigned)(stepc - 3); stepc -= 4;
+        }
+        if (lane < N) {
+            if (lane < nc) b = b * L[sn_col(base, lane, N) + lane];    // the diagonal holds 1 / d
+            xs[xi] = b;
+        }
+        __syncwarp();
+    }
+}
+#endif
+
 // generic variant (fronts wider than a warp): one warp, column-parallel scatter per front row
 __device__ B_FN void b_backward_fronts(const BatchPlan &P, const double *L, double *xs)
 {
@@ -741,21 +792,37 @@ struct BVec {       // shared-memory vectors of one instance
     double *K, *red, *ucol;
     unsigned char *act, *acto;
 };
-__device__ __forceinline__ void b_ls_contrib(const double *delta, const double *alpha, int iz, double &da, double &db)
+__device__ __forceinline__ void b_ls_contrib2(double d, double al, double &da, double &db)
 {   // linesearch.c:133-141
-    const double d = delta[iz], al = alpha[iz];
     if (d > 0.0) { da = d * d; db = -(d * al); }
     else { da = -(d * d); db = d * al; }
 }
-template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V)
+// breakpoint k of the linesearch (linesearch.c:28-39,82-114): slope change delta_k and offset alpha_k
+__device__ __forceinline__ void b_ls_da(const BVec &V, int m, int k, double &dl, double &al)
+{
+    const int i = k < m ? k : k - m;
+    double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
+    const double c0 = V.Adx[i] + (-1.0) * tm;
+    dl = c0 * V.smu[i];
+    if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
+    else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
+}
+// SEP: the scratch lives in vectors that are dead during the linesearch instead of the L area -- keys in
+// [rp, rpi, tm, ucol] (contiguous), 16-bit indices in [rdi, tn], delta / alpha recomputed where they are needed --
+// so that L survives the step and an unchanged K need not be factored again.
+__shared__ int s_ls_kmin, s_ls_cw[8 * BNW];
+__shared__ double s_ls_wa[BNW], s_ls_wb[BNW], s_ls_tau;
+#define B_LS_CONTRIB(iz_, da_, db_) do { double dl_, al_; const int z_ = (int)(iz_); if (SEP) b_ls_da(V, m, z_, dl_, al_); else { dl_ = delta[z_]; al_ = alpha[z_]; } b_ls_contrib2(dl_, al_, da_, db_); } while (0)
+template <int RLMAX, bool SEP> __device__ __forceinline__ double b_linesearch(const BatchPlan &P, const BVec &V)
 {
     const int tid = threadIdx.x, n = P.n, m = P.m, M2 = 2 * m, P2 = P.P2, lane = tid & 31, wid = tid >> 5;
     double *delta = V.K, *alpha = V.K + M2;
-    unsigned long long *key = (unsigned long long *)(V.K + 2 * M2);
-    int *idx = (int *)(key + P2);
+    unsigned long long *key = SEP ? (unsigned long long *)V.rp : (unsigned long long *)(V.K + 2 * M2);
+    typedef typename std::conditional<SEP, unsigned short, int>::type idx_t;
+    idx_t *idx = SEP ? (idx_t *)V.rdi : (idx_t *)(key + P2);
     double *red = V.red;
-    __shared__ int kmin;
-    __shared__ double wa[BNW], wb[BNW], tau_sh;
+    int &kmin = s_ls_kmin;                      // file-scope statics: shared by all instantiations
+    double (&wa)[BNW] = s_ls_wa, (&wb)[BNW] = s_ls_wb, &tau_sh = s_ls_tau;
     double s[4] = {0, 0, 0, 0};
     B_LOOP1
     for (int i = tid; i < m; i += BNT) {
@@ -791,7 +858,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
     // bitonic network only spans next_pow2(nL) slots instead of next_pow2(2m); (key, idx) is a total order,
     // the sorted prefix does not depend on where the pairs started
     const bool compact = P2 <= RLMAX * BNT;
-    __shared__ int cw[RLMAX * BNW];
+    int *cw = s_ls_cw;
     unsigned long long kreg[RLMAX];
     int lpre[RLMAX];
 #pragma unroll
@@ -801,13 +868,9 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
         if (k < P2) {
             unsigned long long kk = ~0ull;
             if (k < M2) {                          // linesearch.c:28-39,82-114
-                const int i = k < m ? k : k - m;
-                double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
-                double c0 = V.Adx[i] + (-1.0) * tm;
-                double dl = c0 * V.smu[i], al;
-                if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
-                else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
-                delta[k] = dl; alpha[k] = al;
+                double dl, al;
+                b_ls_da(V, m, k, dl, al);
+                if (!SEP) { delta[k] = dl; alpha[k] = al; }
                 const double t = b_quot(al, dl);
                 const bool L = t > 0.0, Pp = dl > 0.0;
                 if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
@@ -817,26 +880,22 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
                 const unsigned bal = __ballot_sync(0xffffffffu, kk != ~0ull);
                 kreg[r] = kk; lpre[r] = __popc(bal & ((1u << lane) - 1u));
                 if (lane == 0) cw[r * BNW + wid] = __popc(bal);
-            } else { key[k] = kk; idx[k] = k < M2 ? k : 0; }
+            } else { key[k] = kk; idx[k] = (idx_t)(k < M2 ? k : 0); }
         } else if (compact && lane == 0) cw[r * BNW + wid] = 0;
     }
     B_LOOP1
     for (int k = tid + RLMAX * BNT; k < P2; k += BNT) {    // only when !compact (2m > RLMAX * BNT / 2 ... large m)
         unsigned long long kk = ~0ull;
         if (k < M2) {
-            const int i = k < m ? k : k - m;
-            double tm = V.dy[i] * V.mu[i]; tm = tm * 0.5;
-            double c0 = V.Adx[i] + (-1.0) * tm;
-            double dl = c0 * V.smu[i], al;
-            if (k < m) { dl = dl * (-1.0); al = (V.w[i] + (-1.0) * V.l[i]) * V.smu[i]; }
-            else al = (V.u[i] + (-1.0) * V.w[i]) * V.smu[i];
-            delta[k] = dl; alpha[k] = al;
+            double dl, al;
+            b_ls_da(V, m, k, dl, al);
+            if (!SEP) { delta[k] = dl; alpha[k] = al; }
             const double t = b_quot(al, dl);
             const bool L = t > 0.0, Pp = dl > 0.0;
             if (L != Pp) { r3[0] += dl * dl; r3[1] += dl * al; }
             if (L) { r3[2] += 1.0; kk = (unsigned long long)__double_as_longlong(t); }
         }
-        key[k] = kk; idx[k] = k < M2 ? k : 0;
+        key[k] = kk; idx[k] = (idx_t)(k < M2 ? k : 0);
     }
     block_sum<3>(r3, red);
     const int nLt = (int)(r3[2] + 0.5);
@@ -845,7 +904,8 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
         if (tid == 0) {                        // vec_prod_ind, linesearch.c:190-199
             double pa = 0.0, pb = 0.0;
             for (int k = 0; k < M2; k++) {
-                const double dl = delta[k], al = alpha[k];
+                double dl, al;
+                if (SEP) b_ls_da(V, m, k, dl, al); else { dl = delta[k]; al = alpha[k]; }
                 const bool L = (al / dl) > 0.0, Pp = dl > 0.0;
                 if (L != Pp) { pa += dl * dl; pb += dl * al; }
             }
@@ -867,7 +927,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
             if (r * BNT < P2) {
                 int mine = base;
                 for (int w = 0; w < BNW; w++) { const int c = cw[r * BNW + w]; if (w < wid) mine += c; base += c; }
-                if (kreg[r] != ~0ull) { key[mine + lpre[r]] = kreg[r]; idx[mine + lpre[r]] = tid + r * BNT; }
+                if (kreg[r] != ~0ull) { key[mine + lpre[r]] = kreg[r]; idx[mine + lpre[r]] = (idx_t)(tid + r * BNT); }
             }
         }
         B_LOOP1
@@ -881,7 +941,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
                 const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
                 const bool up = ((lo & size) == 0);
                 const unsigned long long ka = key[lo], kb = key[hi];
-                const int ia = idx[lo], ib = idx[hi];
+                const idx_t ia = idx[lo], ib = idx[hi];
                 const bool gt = (ka > kb) || (ka == kb && ia > ib);
                 if (gt == up) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
             }
@@ -893,7 +953,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
             bool done = false;
             if (nLt == 0 || b + a * __longlong_as_double((long long)key[0]) > 0.0) { tau = -b / a; done = true; }
             for (int i = 0; !done && i < nLt; i++) {
-                double da, db; b_ls_contrib(delta, alpha, idx[i], da, db);
+                double da, db; B_LS_CONTRIB(idx[i], da, db);
                 a = a + da; b = b + db;
                 if (i + 1 < nLt && b + a * __longlong_as_double((long long)key[i + 1]) > 0.0) { tau = -b / a; done = true; }
             }
@@ -908,7 +968,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
     B_LOOP1
     for (int c = 0; c < chunk; c++) {
         const int k = k0 + c;
-        if (k < nLt) { double da, db; b_ls_contrib(delta, alpha, idx[k], da, db); la += da; lb += db; }
+        if (k < nLt) { double da, db; B_LS_CONTRIB(idx[k], da, db); la += da; lb += db; }
     }
     double pa = la, pb = lb;
     for (int o = 1; o < 32; o <<= 1) {
@@ -928,7 +988,7 @@ template <int RLMAX> __device__ __forceinline__ double b_linesearch(const BatchP
         if (k < nLt) {
             const double t = __longlong_as_double((long long)key[k]);
             if (cand_k < 0 && rb + ra * t > 0.0) { cand_k = k; cand_a = ra; cand_b = rb; }
-            double da, db; b_ls_contrib(delta, alpha, idx[k], da, db);
+            double da, db; B_LS_CONTRIB(idx[k], da, db);
             ra += da; rb += db;
         }
     }
@@ -1044,6 +1104,8 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
     double eps_in = P.eps_abs_in, tau = 0.0;
     sigma = P.sigma_init;
     int reset_newton = 1, iter, oter = 0, iter_old = 0, status = QPDO_UNSOLVED, n_active = 0;
+    bool k_valid = false;                       // the L area holds the factor of K(omega, sigma_f)
+    double sigma_f = 0.0;
     B_TICK(0)
     double rpn = 0, rdn = 0, rpin = 0, rdin = 0;
     __syncthreads();
@@ -1178,7 +1240,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                     nch = (int)(cs[0] + 0.5); (void)d1; (void)d2;
                 }
                 if ((proximal && sigma > P.sigma_min) || nch > 25) reset_newton = 1;
-                else if (nch) { FOR_M(k) V.om[k] = V.om[k] + V.tm[k]; }      // ldlupdate_mu_changed (cholmod_interface.c:77-93)
+                else if (nch) { FOR_M(k) V.om[k] = V.om[k] + V.tm[k]; k_valid = false; }      // ldlupdate_mu_changed (cholmod_interface.c:77-93): the factor no longer embodies omega
             }
             if (proximal && oter > 0 && rdn > P.eps_abs && sigma > P.sigma_min) {      // update_sigma (iteration.c:173-180)
                 const double s_old = sigma;
@@ -1215,6 +1277,7 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             if ((reset_newton && n_active) || (n_enter + n_leave) > QPDO_MAX_RANK_UPDATE) { mode = 0; reset_newton = 0; }
             else if (n_active) mode = 1;
             else mode = 2;
+            int om_changed = 0;
             FOR_M(i) {      // row weights embodied in the factor + "dy" = (I+P) res_prim_in ./ mu (newton.c:37-40)
                 const int a = V.act[i], o = V.acto[i];
                 const double mui = V.mu[i], inv = b_rcp(mui);
@@ -1222,21 +1285,34 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
                 if (mode == 0) om = a ? inv : 0.0;
                 else if (mode == 1) { om = V.om[i]; if (a && !o) om = om + inv; if (!a && o) om = om - inv; }
                 else om = 0.0;
+                om_changed |= (om != V.om[i]);
                 V.om[i] = om;
                 V.acto[i] = (unsigned char)a;
                 double v = b_div(V.rpi[i], mui, inv);
                 if (!a) v = v * 2.0;
                 V.dy[i] = v;
             }
-            __syncthreads();
+            // K = Q + sigma I + A' diag(omega) A is the matrix of the last factorization when no row weight and not sigma
+            // has changed since: the factor in the L area is still the one the reference would use (its factor is untouched
+            // when no constraint enters or leaves, src/newton.c:24-33; a refactorization of the same matrix gives the same
+            // bits): assembly and LDL' are skipped, only the two triangular solves run.
+            const bool refactor = __syncthreads_or(om_changed) || !k_valid || sigma != sigma_f;
             b_spmv_At(P, V.Av, V.dy, V.Atdy);
             B_TICK(2)
-            b_assemble(P, V.Av, V.Qv, V.om, sigma, V.K);            // ends with __syncthreads
+            if (refactor) b_assemble(P, V.Av, V.Qv, V.om, sigma, V.K);            // ends with __syncthreads
+            else __syncthreads();
             FOR_N(k) { const int o = P.perm[k]; V.tn[k] = -V.rdi[o] - V.Atdy[o]; }     // P * rhs (newton.c:43-45)
             __syncthreads();
             B_TICK(3)
             if (P.mode == 1) {
-                b_factor_fronts(P, V.K, V.tn, V.ucol);
+#ifndef B_EXACT_PIVOTS
+                if (!refactor) { if (tid < 32) b_forward_sn(P, V.K, V.tn); __syncthreads(); }
+                else
+#endif
+                {
+                    b_factor_fronts(P, V.K, V.tn, V.ucol);
+                    k_valid = P.ls_sep != 0; sigma_f = sigma;         // L survives the step only when the linesearch scratch lives elsewhere
+                }
                 B_TICK(4)
                 if (tid < 32) { if (P.max_front <= SN_NMAX && P.nsuper <= SN_DESC_MAX && P.nSrow <= SN_ROWS_MAX) b_backward_sn(P, V.K, V.tn); else b_backward_fronts(P, V.K, V.tn); }
                 __syncthreads();
@@ -1257,7 +1333,8 @@ __device__ __forceinline__ void b_solve_instance(const BatchPlan &P, const Batch
             __syncthreads();
             B_TICK(6)
             // breakpoint passes unrolled to what 2m needs (the unrolled code of unused passes costs instruction fetch)
-            tau = P.P2 <= 2 * BNT ? b_linesearch<2>(P, V) : P.P2 <= 4 * BNT ? b_linesearch<4>(P, V) : b_linesearch<8>(P, V);
+            if (P.ls_sep) tau = P.P2 <= 2 * BNT ? b_linesearch<2, true>(P, V) : P.P2 <= 4 * BNT ? b_linesearch<4, true>(P, V) : b_linesearch<8, true>(P, V);
+            else tau = P.P2 <= 2 * BNT ? b_linesearch<2, false>(P, V) : P.P2 <= 4 * BNT ? b_linesearch<4, false>(P, V) : b_linesearch<8, false>(P, V);
             FOR_N(i) { V.x[i] = V.x[i] + tau * V.dx[i]; V.Qx[i] = V.Qx[i] + tau * V.Qdx[i]; V.Aty[i] = V.Aty[i] + tau * V.Atdy[i]; }
             FOR_M(i) { V.y[i] = V.y[i] + tau * V.dy[i]; V.Ax[i] = V.Ax[i] + tau * V.Adx[i]; }
             __syncthreads();
@@ -1298,11 +1375,12 @@ __global__ void __launch_bounds__(BNT, B_MINCTAS) k_batch_solve(const B_GC Batch
     TAKE(V.q, n) TAKE(V.x, n) TAKE(V.xbar, n) TAKE(V.Qx, n) TAKE(V.Aty, n) TAKE(V.dx, n) TAKE(V.Qdx, n) TAKE(V.Atdy, n)
     TAKE(V.df, n) TAKE(V.rdi, n) TAKE(V.tn, n) TAKE(V.D, n)
     TAKE(V.l, m) TAKE(V.u, m) TAKE(V.y, m) TAKE(V.ybar, m) TAKE(V.Ax, m) TAKE(V.dy, m) TAKE(V.Adx, m) TAKE(V.w, m)
-    TAKE(V.rp, m) TAKE(V.rpo, m) TAKE(V.rpi, m) TAKE(V.mu, m) TAKE(V.smu, m) TAKE(V.om, m) TAKE(V.E, m) TAKE(V.tm, m)
+    TAKE(V.rpo, m) TAKE(V.mu, m) TAKE(V.smu, m) TAKE(V.om, m) TAKE(V.E, m)
+    TAKE(V.rp, m) TAKE(V.rpi, m) TAKE(V.tm, m)              // [rp, rpi, tm, ucol]: dead during the linesearch, its key area when P.ls_sep
 #undef TAKE
+    V.ucol = p; p += 2 * SN_PW * P.ucolw;
     V.K = p; p += P.karea;
     V.red = p; p += BNW * 8;
-    V.ucol = p; p += 2 * SN_PW * P.ucolw;
     V.act = (unsigned char *)p; V.acto = V.act + m;
     if (P.nsuper <= SN_DESC_MAX) for (int t = threadIdx.x; t < 2 * P.nsuper; t += BNT) s_desc[t] = P.sn_desc[t];
     if (P.nSrow <= SN_ROWS_MAX) for (int t = threadIdx.x; t < P.nSrow; t += BNT) s_rows[t] = P.Srow[t];
@@ -1616,7 +1694,14 @@ extern "C" int qpdo_batch_create(qpdo_batch **out, int n, int m, const int *Qp, 
         P.mode = mode; P.nsuper = S->nsuper; b->mode = mode; P.max_front = max_front; P.ucolw = std::max(max_front + 2, SN_W); P.nSrow = (int)Srow.size();
         int P2 = 64; while (P2 < 2 * m) P2 <<= 1;
         P.P2 = P2;
-        P.karea = std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
+        // linesearch scratch outside the L area when the dead vectors hold it (keys: [rp, rpi, tm, ucol]; 16-bit
+        // indices: [rdi, tn]): L then survives the step and an unchanged K is not factored again
+        P.ls_sep = (mode == 1 && max_front <= SN_NMAX && S->nsuper <= SN_DESC_MAX && (int)Srow.size() <= SN_ROWS_MAX &&
+                    P2 <= 3 * m + 2 * SN_PW * P.ucolw && P2 <= 8 * n && !getenv("QPDO_BATCH_NO_LS_SEP")) ? 1 : 0;
+#ifdef B_EXACT_PIVOTS
+        P.ls_sep = 0;                                    // the exact variant keeps d on the diagonal and always refactors
+#endif
+        P.karea = P.ls_sep ? P.nKpack : std::max(P.nKpack, 4 * m + P2 + P2 / 2 + 2);
         P.ellA.nround = (int)ellRound[0].size(); P.ellAt.nround = (int)ellRound[1].size(); P.ellQ.nround = (int)ellRound[2].size();
         if (b_upload(b, &P.ellA.round, ellRound[0]) || b_upload(b, &P.ellA.rec, ellRec[0]) || b_upload(b, &P.ellAt.round, ellRound[1]) ||
             b_upload(b, &P.ellAt.rec, ellRec[1]) || b_upload(b, &P.ellQ.round, ellRound[2]) || b_upload(b, &P.ellQ.rec, ellRec[2])) break;
