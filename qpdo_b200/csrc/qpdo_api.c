@@ -222,6 +222,16 @@ static c_float *vdup(const c_float *a, size_t n)
     return b;
 }
 
+/* work->data->{q, l, u} mirror the SCALED vectors the device works on, like the reference's work->data after
+ * scale_data (src/scaling.c:40-91; qpdo_mex.c reads them); work->data->Q / A keep the caller's values and layout --
+ * their scaled copies live in HBM only (32-bit CSC, sorted). */
+static void mirror_data_vectors(QPDOWorkspace *work)
+{
+    qpdo_dev *dev = DEV(work);
+    if (work->data->n) qpdo_dev_get_vector(dev, "q", work->data->q, (long)work->data->n);
+    if (work->data->m) { qpdo_dev_get_vector(dev, "l", work->data->l, (long)work->data->m); qpdo_dev_get_vector(dev, "u", work->data->u, (long)work->data->m); }
+}
+
 /* ------------------------------------------------------------------ qpdo_setup ------------ */
 QPDOWorkspace *qpdo_setup(const QPDOData *data, const QPDOSettings *settings)
 {
@@ -299,6 +309,7 @@ QPDOWorkspace *qpdo_setup(const QPDOData *data, const QPDOSettings *settings)
         work->scaling = QPDO_NULL;
         if (qpdo_dev_get_scaling(dev, NULL, NULL, NULL, NULL, NULL, NULL, &work->norm_q)) goto fail;
     }
+    mirror_data_vectors(work);
     work->chol->linsys_rhs = dense_shim(n, &work->linsys_rhs);
     work->chol->dx = dense_shim(n, &work->dx);
     work->chol->dy = dense_shim(m, &work->dy);
@@ -483,6 +494,7 @@ void qpdo_update_settings(QPDOWorkspace *work, const QPDOSettings *settings)
             update_status(work->info, QPDO_ERROR);
             return;
         }
+        mirror_data_vectors(work);
     }
     free(work->settings);
     work->settings = copy_settings(settings);
@@ -506,11 +518,7 @@ void qpdo_update_bounds(QPDOWorkspace *work, const c_float *l, const c_float *u)
         return;
     }
     /* host mirror of the (scaled) bounds, qpdo.c:538-543 */
-    for (j = 0; j < m; j++) {
-        c_float e = work->settings->scaling ? work->scaling->E[j] : 1.0;
-        if (l) work->data->l[j] = work->settings->scaling ? e * l[j] : l[j];
-        if (u) work->data->u[j] = work->settings->scaling ? e * u[j] : u[j];
-    }
+    mirror_data_vectors(work);
 }
 
 /* ------------------------------------------------------------------ qpdo_update_q --------- */
@@ -525,6 +533,7 @@ void qpdo_update_q(QPDOWorkspace *work, const c_float *q)
     work->sigma = sigma;
     work->norm_q = nq;
     if (work->settings->scaling) { work->scaling->c = c; work->scaling->cinv = cinv; }
+    mirror_data_vectors(work);                  /* scaled q, qpdo.c:560-571 */
 }
 
 /* ------------------------------------------------------------------ qpdo_cleanup ---------- */

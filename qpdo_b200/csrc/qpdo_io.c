@@ -131,7 +131,7 @@ void qpdo_free_data(QPDOData *d)
 }
 
 /* ------------------------------------------------------------------ the reader */
-enum { S_NONE, S_ROWS, S_COLUMNS, S_RHS, S_RANGES, S_BOUNDS, S_QUADOBJ, S_QMATRIX, S_SKIP };
+enum { S_NONE, S_ROWS, S_COLUMNS, S_RHS, S_RANGES, S_BOUNDS, S_QUADOBJ, S_QMATRIX, S_OBJSENSE, S_SKIP };
 
 static int split(char *line, char **tok, int maxtok)
 {
@@ -178,10 +178,19 @@ int qpdo_read_qps(const char *path, QPDOData **out, c_int *m_rows, c_int *err_li
             else if (!strcmp(tok[0], "QUADOBJ")) section = S_QUADOBJ;
             else if (!strcmp(tok[0], "QMATRIX")) section = S_QMATRIX;
             else if (!strcmp(tok[0], "ENDATA")) break;
-            else section = S_SKIP;                    /* OBJSENSE, OBJSENSE MAX etc.: not supported, skipped */
+            else if (!strcmp(tok[0], "OBJSENSE")) {
+                /* "OBJSENSE MAX" on the header line, or MAX / MIN on the next data line: QPDO minimises; a maximisation
+                 * file is rejected with its line number instead of being solved as a minimisation */
+                section = S_OBJSENSE;
+                if (nt > 1 && (!strcmp(tok[1], "MAX") || !strcmp(tok[1], "MAXIMIZE"))) FAIL(-2);
+            }
+            else section = S_SKIP;                    /* OBJSENSE_MAXIMIZE-style extensions of other dialects etc.: skipped */
             continue;
         }
         switch (section) {
+        case S_OBJSENSE:
+            if (!strcmp(tok[0], "MAX") || !strcmp(tok[0], "MAXIMIZE")) FAIL(-2);
+            break;
         case S_ROWS: {
             if (nt < 2) FAIL(-2);
             const long before = rows.count, r = names_add(&rows, tok[1]);

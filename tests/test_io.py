@@ -68,6 +68,25 @@ def test_read_qps_errors(cuda_lib, tmp_path):
         qio.read_qps(bad, cuda_lib)
 
 
+def test_read_qps_objsense(cuda_lib, tmp_path):
+    """OBJSENSE MIN (either spelling) is accepted; a maximisation file is rejected with its line number instead of
+    being read -- and solved -- as a minimisation"""
+    ok1 = tmp_path / "min1.qps"
+    ok1.write_text(QPS.replace("ROWS\n", "OBJSENSE\n    MIN\nROWS\n", 1))
+    ok2 = tmp_path / "min2.qps"
+    ok2.write_text(QPS.replace("ROWS\n", "OBJSENSE MIN\nROWS\n", 1))
+    for f in (ok1, ok2):
+        np.testing.assert_array_equal(qio.read_qps(f, cuda_lib)["q"], [1.5, -2.0, 0.5, 0.0])
+    bad1 = tmp_path / "max1.qps"
+    bad1.write_text(QPS.replace("ROWS\n", "OBJSENSE\n    MAX\nROWS\n", 1))
+    with pytest.raises(ValueError, match="line 3"):
+        qio.read_qps(bad1, cuda_lib)
+    bad2 = tmp_path / "max2.qps"
+    bad2.write_text(QPS.replace("ROWS\n", "OBJSENSE MAX\nROWS\n", 1))
+    with pytest.raises(ValueError, match="line 2"):
+        qio.read_qps(bad2, cuda_lib)
+
+
 def test_read_qps_solves_on_the_oracle(cuda_lib, oracle_mod, qps_file):
     d = qio.read_qps(qps_file, cuda_lib)
     o = oracle_mod.solve(d, trace=False)

@@ -354,3 +354,29 @@ def test_update_settings_more_scaling_sweeps_intended_total_scaling(cuda_lib, mo
     assert b.status_val == 1
     assert rel_err(b.x, a.x) <= 1e-4 and abs(b.objective - a.objective) <= 1e-6 * abs(a.objective)
     s.delete()
+
+
+def test_host_mirror_of_the_scaled_data_matches_the_reference(oracle_mod):
+    """work->data->{q, l, u} hold the SCALED vectors after qpdo_setup, qpdo_update_bounds and qpdo_update_q, as in the
+    reference (src/scaling.c:40-91, src/qpdo.c:538-543, 560-571): same values as the live reference's workspace"""
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref not built")
+    p = problems.random_qp(120, 80, 0.08, seed=11)
+    g = gpu_solver()
+    r = capi.Solver(oracle_mod.ref_library())
+    n, m = 120, 80
+
+    def vecs(s):
+        d = s.work.data.contents
+        f = lambda ptr, k: np.array(np.ctypeslib.as_array(ptr, shape=(k,)))
+        return f(d.q, n), f(d.l, m), f(d.u, m)
+    for s in (g, r):
+        s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+    for a, b in zip(vecs(g), vecs(r)):
+        assert rel_err(b, a) <= 1e-13
+    for s in (g, r):
+        s.update_bounds(p["l"] - 0.25, p["u"] + 0.5)
+        s.update_q(p["q"] * 1.25 + 0.125)
+    for a, b in zip(vecs(g), vecs(r)):
+        assert rel_err(b, a) <= 1e-13
+    g.delete(); r.delete()
