@@ -33,6 +33,7 @@ struct Factor {
     int *sn_start = nullptr, *sn_nr = nullptr, *rows = nullptr, *rel = nullptr, *sn_parent = nullptr;
     int *child_ptr = nullptr, *child_idx = nullptr, *level_sn = nullptr;
     int64_t *sn_rowptr = nullptr, *Lp = nullptr, *Up = nullptr;
+    void *fdesc = nullptr;           // FrontDesc per supernode (factor.cu)
     int *perm = nullptr, *pinv = nullptr;
     int *Ki = nullptr, *Kp = nullptr, *Kq = nullptr, *Kt_row = nullptr, *Kt_a1 = nullptr, *Kt_a2 = nullptr;
     int *Kcol = nullptr;             // column of each K entry (diagonal test)
@@ -53,6 +54,7 @@ struct Factor {
     int *cnt = nullptr, *cnt_host = nullptr;      // support / outside counters
     int ordering = 1, npattern = 0, analyses = 0;
     bool dynamic = false, full = false;
+    bool panel_v1 = false;                        // QPDO_B200_PANEL=v1: round-1 panel step (A/B measurements)
 };
 
 struct qpdo_dev {

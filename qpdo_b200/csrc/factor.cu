@@ -22,7 +22,9 @@
 #define TS 64          // SYRK tile
 #define PLD 36         // padded leading dimension of a 64 x 32 panel tile in smem (conflict free)
 
+struct FrontDesc { int64_t Lp, Up; int nc, nr; };        // one per supernode: what a front kernel needs to find its data
 struct FArgs {
+    const FrontDesc *fdesc;
     const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
     const int64_t *sn_rowptr, *Lp, *Up;
     double *Lx, *Ux;
@@ -189,155 +191,19 @@ __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
         __syncthreads();
     }
 }
-// LDL' of the nb x nb diagonal block at (kb, kb): unit lower L11, D on the diagonal.  ONE warp per front,
-// lane = block row with its 32 entries in registers; the pivot and the scaled column travel by shuffle, so
-// the 32-pivot chain has no barrier and no shared-memory round trip (the chain, not the flops, is what a
-// lone CTA at the top of the tree pays for).  Per entry the fma sequence is ascending k, as everywhere.
-__global__ void __launch_bounds__(32) k_big_potrf(FArgs A, const int *list, int kb)
-{
-    const int s = list[blockIdx.x];
-    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
-    if (kb >= nc) return;
-    const int nb = min(NB, nc - kb), lane = threadIdx.x;
-    double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N + kb;
-    double a[NB];
-#pragma unroll
-    for (int j = 0; j < NB; j++) a[j] = (j < nb && lane < nb && lane >= j) ? Lb[(int64_t)j * N + lane] : (lane == j ? 1.0 : 0.0);
-    bool bad = false;
-#pragma unroll
-    for (int k = 0; k < NB; k++) {
-        const double dk = __shfl_sync(0xffffffffu, a[k], k);
-        bad = bad || (k < nb && !(dk > 0.0));
-        const double ak = a[k];
-        const double l = div_by_pivot(ak, dk, __drcp_rn(dk));
-#pragma unroll
-        for (int j = k + 1; j < NB; j++) {
-            const double lj = __shfl_sync(0xffffffffu, l, j);
-            a[j] = fma(-ak, lj, a[j]);                   // rows above the diagonal carry garbage that is never stored
-        }
-        if (lane > k) a[k] = l;
-    }
-    if (bad && lane == 0) A.sc->not_posdef = 1;
-#pragma unroll
-    for (int j = 0; j < NB; j++)
-        if (j < nb && lane < nb) Lb[(int64_t)j * N + lane] = (lane >= j) ? a[j] : 0.0;
-}
-// rows below the diagonal block: X <- X L11^{-T} D^{-1}, one row per thread
-__global__ void __launch_bounds__(128) k_big_trsm(FArgs A, const int *list, int kb)
-{
-    __shared__ double D[NB][NB + 1];
-    const int s = list[blockIdx.x];
-    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
-    if (kb >= nc) return;
-    const int nb = min(NB, nc - kb), tid = threadIdx.x;
-    const int r0 = kb + nb + blockIdx.y * 128;
-    if (r0 >= N) return;
-    double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N;
-    for (int idx = tid; idx < NB * NB; idx += 128) {
-        int j = idx / NB, i = idx - j * NB;
-        D[i][j] = (i < nb && j < nb) ? Lb[(int64_t)j * N + kb + i] : (i == j ? 1.0 : 0.0);
-    }
-    __shared__ double Rinv[NB];
-    __syncthreads();
-    if (tid < NB) Rinv[tid] = __drcp_rn(D[tid][tid]);
-    __syncthreads();
-    const int i = r0 + tid;
-    if (i >= N) return;
-    double x[NB];
-#pragma unroll
-    for (int j = 0; j < NB; j++) x[j] = (j < nb) ? Lb[(int64_t)j * N + i] : 0.0;
-    // W = B L11^{-T} (unit lower L11), then X = W D^{-1}
-#pragma unroll
-    for (int j = 0; j < NB; j++) {
-        double v = x[j];
-#pragma unroll
-        for (int k = 0; k < j; k++) v = fma(-x[k], D[j][k], v);
-        x[j] = v;
-    }
-#pragma unroll
-    for (int j = 0; j < NB; j++) x[j] = div_by_pivot(x[j], D[j][j], Rinv[j]);
-#pragma unroll
-    for (int j = 0; j < NB; j++) if (j < nb) Lb[(int64_t)j * N + i] = x[j];
-}
 // trailing update C -= (X D) X' for the lower 64 x 64 tiles, X = panel rows x nb; FP64 tensor pipe
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b)
 {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
-__global__ void __launch_bounds__(256) k_big_syrk(FArgs A, const int *list, int kb)
-{
-    __shared__ double Pa[TS * PLD], Pb[TS * PLD];
-    const int s = list[blockIdx.x];
-    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
-    if (kb >= nc) return;
-    const int nb = min(NB, nc - kb);
-    const int r0 = kb + nb, R = N - r0;
-    if (R <= 0) return;
-    const int nt = (R + TS - 1) / TS;
-    int ti = (int)((sqrt(8.0 * blockIdx.y + 1.0) - 1.0) * 0.5);
-    while ((ti + 1) * (ti + 2) / 2 <= (int)blockIdx.y) ti++;
-    while (ti * (ti + 1) / 2 > (int)blockIdx.y) ti--;
-    const int tj = blockIdx.y - ti * (ti + 1) / 2;
-    if (ti >= nt) return;
-    const int tid = threadIdx.x;
-    const double *Lb = A.Lx + A.Lp[s] + (int64_t)kb * N;
-    const int ra = r0 + ti * TS, rb = r0 + tj * TS;
-    for (int idx = tid; idx < TS * NB; idx += 256) {
-        int k = idx / TS, r = idx - k * TS;                 // consecutive threads -> consecutive rows
-        Pa[r * PLD + k] = (k < nb && ra + r < N) ? Lb[(int64_t)k * N + ra + r] * Lb[(int64_t)k * N + kb + k] : 0.0;
-        Pb[r * PLD + k] = (k < nb && rb + r < N) ? Lb[(int64_t)k * N + rb + r] : 0.0;
-    }
-    __syncthreads();
-    const int lane = tid & 31, wid = tid >> 5;
-    const int wr = (wid & 1) * 32, wc = (wid >> 1) * 16;    // warp tile: 32 rows x 16 cols
-    const int g = lane >> 2, q = lane & 3;
-    double acc[4][2][2];
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 2; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
-#pragma unroll
-    for (int ks = 0; ks < NB / 4; ks++) {
-        double af[4], bf[2];
-#pragma unroll
-        for (int a = 0; a < 4; a++) af[a] = Pa[(wr + a * 8 + g) * PLD + ks * 4 + q];
-#pragma unroll
-        for (int b = 0; b < 2; b++) bf[b] = Pb[(wc + b * 8 + g) * PLD + ks * 4 + q];
-#pragma unroll
-        for (int a = 0; a < 4; a++)
-#pragma unroll
-            for (int b = 0; b < 2; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
-    }
-    // read-modify-write of the 16 destination entries: all loads first (one round trip), then the stores
-    double *dst[4][2][2];
-    double cur[4][2][2];
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 2; b++)
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                const int gi = ra + wr + a * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
-                dst[a][b][e] = (gi < N && gj <= gi) ? front_elem(A, s, nc, nr, N, gi, gj) : nullptr;
-                cur[a][b][e] = dst[a][b][e] ? *dst[a][b][e] : 0.0;
-            }
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 2; b++)
-#pragma unroll
-            for (int e = 0; e < 2; e++)
-                if (dst[a][b][e]) *dst[a][b][e] = cur[a][b][e] - acc[a][b][e];
-}
-
 // One launch per 32-pivot panel step of a big front: every CTA (front, tile pair) redoes the LDL' of the
 // diagonal block (one warp, registers) and the triangular solve of ITS two 64-row tiles from the raw panel,
 // then applies the rank-32 update of its 64 x 64 tile on the FP64 tensor pipe.  The factored panel goes to
 // Xout (tile pairs with tj == 0 write their rows, pair 0 the diagonal block), the raw panel in Lx stays
 // intact for the other CTAs -- so potrf -> trsm -> syrk needs no grid-wide ordering, and the serial chain of
 // the tree top pays one launch per panel instead of three.  Arithmetic identical to the three-kernel path.
-__global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int kb)
+__global__ void __launch_bounds__(256) k_big_panel_v1(FArgs A, const int *list, int kb)
 {
     __shared__ double Pa[TS * PLD], Pb[TS * PLD];
     __shared__ double D[NB][NB + 1];
@@ -460,12 +326,317 @@ __global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int
                 if (dst[a][b][e]) *dst[a][b][e] = cur[a][b][e] - acc[a][b][e];
 }
 
+
+// ---- panel step, second generation -----------------------------------------------------------------
+// Same ownership as above (CTA = front x tile pair, every CTA factors the diagonal block itself, no grid-wide
+// ordering), but the step is built so that nothing avoidable sits on the serial chain of the tree top:
+//  * front descriptors arrive as kernel parameters when the launch has few fronts (the top of the tree): no chain of
+//    dependent global loads (list -> sn_start -> Lp -> data) before the first useful load is issued;
+//  * warp 0 fetches the diagonal block first; warps 2..7 stage the two raw 64 x 32 row tiles into shared memory by
+//    cp.async (k-major, ld 68: the DMMA fragment loads below are bank-conflict free) and every warp fetches its part
+//    of the CTA's 64 x 64 tile of the trailing matrix into registers, so both L2 round trips hide behind the LDL';
+//  * warp 0 factors the 32 x 32 diagonal block with its rows in registers; the pivot column travels through one
+//    shared-memory row per step (one 8-byte store, broadcast 16-byte loads) instead of 2 x 31 shuffles; the column
+//    of the NEXT step is published and the next reciprocal (branch-free, rcp_pivot) started before the rest of the
+//    current update is issued;
+//  * warp 1 follows one step behind (one mbarrier per pivot column) and builds inv(L11) column by column from the
+//    same shared rows: no extra time on the chain;
+//  * the triangular solve of the row tiles is a product with inv(L11)' on the FP64 tensor pipe (20 of the 32
+//    k-steps per 8 x 8 block: the zero blocks of the triangle are skipped), Y = B inv(L11)' feeds the update as
+//    X D, X = Y D^-1 is the panel;
+//  * rank-32 update of the 64 x 64 tile by DMMA as before;
+//  * CTA y == 0 of a front has no tile: it writes the factored diagonal block, with inv(L11) (strictly lower part,
+//    transposed) in its unused upper triangle -- the triangular solves use it (k_fwd / k_bwd: no substitution chain
+//    in blocked fronts) -- and leaves; the tile pairs start at y == 1.
+#define TSP 68         // leading dimension of a k-major 32 x 64 tile (68 mod 16 == 4)
+#define LDI 36         // leading dimension of the k-major inverse (36 mod 16 == 4)
+#define PANEL_SMEM ((2 * NB * TSP + NB * NB + NB * LDI + NB + NB) * sizeof(double))
+#define PANEL_PARAM_FRONTS 16
+struct PanelFronts { int count; FrontDesc d[PANEL_PARAM_FRONTS]; };
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async8(double *dst_smem, const double *src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" :: "r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_lane0(unsigned long long *bar, int lane)
+{
+    asm volatile("{\n.reg .pred P1;\nsetp.eq.s32 P1, %1, 0;\n@P1 mbarrier.arrive.shared::cta.b64 _, [%0];\n}\n" :: "r"(smem_u32(bar)), "r"(lane) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n.reg .pred P1;\nWAIT_LOOP:\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n@P1 bra DONE;\nbra WAIT_LOOP;\nDONE:\n}\n"
+                 :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1 / d to an ulp without the range check (and branch) of __drcp_rn: MUFU.RCP64H seed (2^-20), one cubic step;
+// pivots of a regularised SPD matrix are nowhere near the denormal / overflow ranges the check is for
+__device__ __forceinline__ double rcp_pivot(double d)
+{
+    double x;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+    const double e = fma(-d, x, 1.0);
+    const double e2 = fma(e, e, e);
+    return fma(x, e2, x);
+}
+#ifdef PANEL_PROBE
+// -DPANEL_PROBE: the first tile CTA of front 0 of every panel launch records SM-clock stamps of its phases and the
+// global timer at entry / exit (tools/probe_panel.py)
+#define NPROBE 16
+__device__ long long g_probe[NPROBE * 4096];
+__device__ int g_probe_n;
+#define PROBE(i) do { if (probe_on) pr[i] = clock64(); } while (0)
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+extern "C" int qpdo_dev_probe_read(long long *out, int cap)
+{
+    int n = 0;
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&n, g_probe_n, sizeof(int));
+    n = n < cap ? n : cap;
+    if (n > 4096) n = 4096;
+    if (n > 0) cudaMemcpyFromSymbol(out, g_probe, sizeof(long long) * NPROBE * n);
+    int zero = 0;
+    cudaMemcpyToSymbol(g_probe_n, &zero, sizeof(int));
+    return n;
+}
+#else
+#define PROBE(i)
+#endif
+__global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int kb, const __grid_constant__ PanelFronts PF)
+{
+    extern __shared__ __align__(16) double psm[];
+    double *Ta = psm, *Tb = Ta + NB * TSP, *Us = Tb + NB * TSP, *LiT = Us + NB * NB, *Rinv = LiT + NB * LDI;
+    unsigned long long *bars = (unsigned long long *)(Rinv + NB);
+#ifdef PANEL_PROBE
+    const bool probe_on = blockIdx.x == 0 && blockIdx.y == 1 && (threadIdx.x & 31) == 0;
+    __shared__ long long pr[NPROBE];
+    if (probe_on && threadIdx.x == 0) { pr[14] = gtimer(); }
+    PROBE(0);
+#endif
+    FrontDesc fd;
+    if (PF.count) fd = PF.d[blockIdx.x]; else fd = A.fdesc[list[blockIdx.x]];
+    const int nc = fd.nc, nr = fd.nr, N = nc + nr;
+    if (kb >= nc) return;
+    const int nb = min(NB, nc - kb);
+    const int r0 = kb + nb, R = N - r0;
+    const int nt = (R + TS - 1) / TS;
+    const bool writer = blockIdx.y == 0;                     // diagonal block out, no tile
+    const int pair = writer ? 0 : (int)blockIdx.y - 1;
+    int ti = (int)((sqrtf(8.0f * pair + 1.0f) - 1.0f) * 0.5f);
+    while ((ti + 1) * (ti + 2) / 2 <= pair) ti++;
+    while (ti * (ti + 1) / 2 > pair) ti--;
+    const int tj = pair - ti * (ti + 1) / 2;
+    if (!writer && ti >= nt) return;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    double *Lfront = A.Lx + fd.Lp, *Ufront = A.Ux + fd.Up;
+    const double *Lraw = Lfront + (int64_t)kb * N;                  // raw panel, column k at Lraw + k * N
+    double *Xo = A.Xout + fd.Lp + (int64_t)kb * N;
+    const int ra = r0 + ti * TS, rb = r0 + tj * TS;
+    const bool diag_tile = (ti == tj);
+    if (tid == 0) PROBE(1);
+    // ---- warp 0: the diagonal block first (lane = row, a[j] = entry (lane, j)); the loads fly while the addresses of
+    // the destination tile are worked out, the identity padding beyond nb is applied when they are first used
+    double a[NB];
+    if (wid == 0) {
+        const double *pd = Lraw + kb + min(lane, nb - 1);
+#pragma unroll
+        for (int j = 0; j < NB; j++) a[j] = pd[(int64_t)min(j, nb - 1) * N];
+        mbar_init(bars + lane, 1);
+    }
+    // ---- destination tile of the update into registers (L2 round trip hidden behind the LDL'): column bases, then rows
+    const int wr = (wid & 1) * 32, wc = (wid >> 1) * 16;    // warp tile of the update: 32 rows x 16 cols
+    double *colp[2][2];
+    double cur[4][2][2];
+    if (!writer) {
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int gj = rb + wc + b * 8 + q * 2 + e;
+                colp[b][e] = (gj < nc) ? (Lfront + (int64_t)gj * N) : (Ufront + (int64_t)(gj - nc) * nr - nc);
+            }
+#pragma unroll
+        for (int a4 = 0; a4 < 4; a4++)
+#pragma unroll
+            for (int b = 0; b < 2; b++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const int gi = ra + wr + a4 * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
+                    const bool ok = gi < N && gj <= gi;
+                    cur[a4][b][e] = *(ok ? (const double *)(colp[b][e] + gi) : Lraw);   // no select on the loaded value: nothing waits here
+                }
+    }
+    if (tid == 0) PROBE(2);
+    __syncthreads();
+    if (tid == 0) PROBE(3);
+    if (wid == 0) {
+        // ---- LDL' of the diagonal block
+        if (nb < NB) {                                          // last panel of a front: identity padding
+#pragma unroll
+            for (int j = 0; j < NB; j++) a[j] = (j < nb && lane < nb) ? a[j] : (lane == j ? 1.0 : 0.0);
+        }
+        Us[lane] = a[0];
+        __syncwarp();
+        mbar_arrive_lane0(bars, lane);
+        double dk = Us[0];
+        double r = rcp_pivot(dk);
+        if (tid == 0) PROBE(4);
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < NB; k++) {
+            const double *uk = Us + k * NB;
+            bad = bad || (k < nb && !(dk > 0.0));
+            const double li = a[k] * r;
+            double dn = 1.0, rn = 1.0;
+            if (lane == k) Rinv[k] = r;
+            if (k + 1 < NB) {                                   // next pivot column first: published, its reciprocal started
+                a[k + 1] = fma(-li, uk[k + 1], a[k + 1]);
+                Us[(k + 1) * NB + lane] = a[k + 1];
+                __syncwarp();
+                mbar_arrive_lane0(bars + k + 1, lane);
+                dn = Us[(k + 1) * NB + k + 1];
+                rn = rcp_pivot(dn);
+            }
+            // the rest of the update is independent of the next reciprocal: the scheduler interleaves the two
+            double u[NB];
+#pragma unroll
+            for (int j = ((k + 2) & ~1); j < NB; j += 2) { const double2 t = *reinterpret_cast<const double2 *>(uk + j); u[j] = t.x; u[j + 1] = t.y; }
+#pragma unroll
+            for (int j = k + 2; j < NB; j++) a[j] = fma(-li, u[j], a[j]);
+            if (lane > k) a[k] = li;
+            dk = dn; r = rn;
+        }
+        if (tid == 0) PROBE(5);
+        if (writer) {
+            if (bad && lane == 0) A.sc->not_posdef = 1;
+#pragma unroll
+            for (int j = 0; j < NB; j++)
+                if (j < nb && lane < nb && lane >= j) Xo[(int64_t)j * N + kb + lane] = a[j];
+        }
+    } else if (wid == 1) {
+        // ---- inv(L11), lane = column c: v[i] = inv(L11)(i, c); right-looking over the pivot columns as they appear
+        // (step k uses column k and 1 / d_k, both published before the arrival on barrier k + 1)
+        double v[NB];
+#pragma unroll
+        for (int i = 0; i < NB; i++) v[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k + 1 < NB; k++) {
+            mbar_wait(bars + k + 1, 0);
+            const double *uk = Us + k * NB;
+            double u[NB];
+#pragma unroll
+            for (int j = ((k + 1) & ~1); j < NB; j += 2) { const double2 t = *reinterpret_cast<const double2 *>(uk + j); u[j] = t.x; u[j + 1] = t.y; }
+            const double sk = Rinv[k] * v[k];
+#pragma unroll
+            for (int i = k + 1; i < NB; i++) v[i] = fma(-u[i], sk, v[i]);
+        }
+        if (tid == 32) PROBE(6);
+        if (writer) {
+#pragma unroll
+            for (int i = 1; i < NB; i++)
+                if (i < nb && lane < i) Xo[(int64_t)i * N + kb + lane] = v[i];
+        } else {
+#pragma unroll
+            for (int i = 0; i < NB; i += 2) *reinterpret_cast<double2 *>(LiT + lane * LDI + i) = make_double2(v[i], v[i + 1]);
+        }
+    } else if (!writer) {
+        // ---- warps 2..7 stage the raw row tiles (k-major) by cp.async while the diagonal block is factored
+        const int t192 = tid - 64;
+        for (int idx = t192; idx < NB * TS; idx += 192) {
+            const int k = idx >> 6, r = idx & 63;
+            if (k < nb && ra + r < N) cp_async8(Ta + k * TSP + r, Lraw + (int64_t)k * N + ra + r); else Ta[k * TSP + r] = 0.0;
+        }
+        if (!diag_tile)
+            for (int idx = t192; idx < NB * TS; idx += 192) {
+                const int k = idx >> 6, r = idx & 63;
+                if (k < nb && rb + r < N) cp_async8(Tb + k * TSP + r, Lraw + (int64_t)k * N + rb + r); else Tb[k * TSP + r] = 0.0;
+            }
+    }
+    if (writer) return;
+    cp_async_wait_all();
+    if (tid == 64) PROBE(7);
+    __syncthreads();
+    if (tid == 0) PROBE(8);
+    // ---- Y = B inv(L11)' for rows 8 wid .. 8 wid + 7 of both tiles (DMMA, triangle blocks only)
+    {
+        double afa[NB / 4], afb[NB / 4];
+#pragma unroll
+        for (int ks = 0; ks < NB / 4; ks++) {
+            afa[ks] = Ta[(4 * ks + q) * TSP + 8 * wid + g];
+            afb[ks] = diag_tile ? 0.0 : Tb[(4 * ks + q) * TSP + 8 * wid + g];
+        }
+        __syncwarp();
+        double ya[4][2], yb[4][2];
+#pragma unroll
+        for (int b = 0; b < 4; b++) { ya[b][0] = ya[b][1] = yb[b][0] = yb[b][1] = 0.0; }
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+#pragma unroll
+            for (int ks = 0; ks < 2 * b + 2; ks++) {
+                const double bf = LiT[(4 * ks + q) * LDI + 8 * b + g];
+                dmma884(ya[b][0], ya[b][1], afa[ks], bf);
+                if (!diag_tile) dmma884(yb[b][0], yb[b][1], afb[ks], bf);
+            }
+        const int r = 8 * wid + g;
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int j = 8 * b + 2 * q + e;
+                const double rj = Rinv[j];
+                const double xa = ya[b][e] * rj;
+                Ta[j * TSP + r] = ya[b][e];
+                Tb[j * TSP + r] = diag_tile ? xa : yb[b][e] * rj;
+                if (tj == 0 && j < nb && ra + r < N) Xo[(int64_t)j * N + ra + r] = xa;
+            }
+    }
+    if (tid == 0) PROBE(9);
+    __syncthreads();
+    if (tid == 0) PROBE(10);
+    // ---- rank-nb update of the 64 x 64 tile (ti, tj): C -= (X D) X'
+    double acc[4][2][2];
+#pragma unroll
+    for (int a4 = 0; a4 < 4; a4++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) acc[a4][b][0] = acc[a4][b][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < NB / 4; ks++) {
+        double af[4], bf[2];
+#pragma unroll
+        for (int a4 = 0; a4 < 4; a4++) af[a4] = Ta[(4 * ks + q) * TSP + wr + a4 * 8 + g];
+#pragma unroll
+        for (int b = 0; b < 2; b++) bf[b] = Tb[(4 * ks + q) * TSP + wc + b * 8 + g];
+#pragma unroll
+        for (int a4 = 0; a4 < 4; a4++)
+#pragma unroll
+            for (int b = 0; b < 2; b++) dmma884(acc[a4][b][0], acc[a4][b][1], af[a4], bf[b]);
+    }
+    if (tid == 0) PROBE(11);
+#pragma unroll
+    for (int a4 = 0; a4 < 4; a4++)
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int gi = ra + wr + a4 * 8 + g, gj = rb + wc + b * 8 + q * 2 + e;
+                if (gi < N && gj <= gi) colp[b][e][gi] = cur[a4][b][e] - acc[a4][b][e];
+            }
+#ifdef PANEL_PROBE
+    if (tid == 0) PROBE(12);
+    if (probe_on && tid == 0) { pr[13] = N; pr[15] = gtimer(); int slot = atomicAdd(&g_probe_n, 1); if (slot < 4096) for (int i = 0; i < NPROBE; i++) g_probe[slot * NPROBE + i] = pr[i]; }
+#endif
+}
+
 // ------------------------------------------------------------------------------- triangular solves
 struct SArgs {
     const int *sn_start, *sn_nr, *rel, *rows, *child_ptr, *child_idx;
     const int64_t *sn_rowptr, *Lp;
     const double *Lx, *Xout;   // fronts of order N > bigN read their panel from Xout
-    int bigN;
+    int bigN, panel_v1;        // panel_v1: no inverse diagonal blocks in Xout (round-1 panel step)
     double *xs, *uv;
 };
 // forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t (unit lower); z_s = D^{-1} y_s is stored;
@@ -495,9 +666,22 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
         __syncthreads();
         if (tid < 32) {
             double v = (lane < nb) ? vec[kb + lane] : 0.0;
-            for (int k = 0; k < nb; k++) {
-                const double yk = __shfl_sync(0xffffffffu, v, k);
-                if (lane > k && lane < nb) v = fma(-D[lane][k], yk, v);
+            if (N > A.bigN && !A.panel_v1) {
+                // blocked fronts carry inv(L11) in the upper triangle of the diagonal block (k_big_panel):
+                // y = inv(L11) t as a 32 x 32 product, four partial sums, no substitution chain
+                double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+                for (int k = 0; k < nb; k += 4) {
+                    if (k < lane) p0 = fma(D[k][lane], vec[kb + k], p0);
+                    if (k + 1 < lane) p1 = fma(D[k + 1][lane], vec[kb + k + 1], p1);
+                    if (k + 2 < lane) p2 = fma(D[k + 2][lane], vec[kb + k + 2], p2);
+                    if (k + 3 < lane) p3 = fma(D[k + 3][lane], vec[kb + k + 3], p3);
+                }
+                v += (p0 + p1) + (p2 + p3);
+            } else {
+                for (int k = 0; k < nb; k++) {
+                    const double yk = __shfl_sync(0xffffffffu, v, k);
+                    if (lane > k && lane < nb) v = fma(-D[lane][k], yk, v);
+                }
             }
             // y feeds the updates below; z = D^{-1} y is what the backward pass starts from
             if (lane < nb) { yb[lane] = v; A.xs[f + kb + lane] = v / D[lane][lane]; }
@@ -563,9 +747,22 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
         __syncthreads();
         if (tid < 32) {
             double v = (lane < nb) ? vec[kb + lane] : 0.0;
-            for (int k = nb - 1; k >= 0; k--) {
-                const double xk = __shfl_sync(0xffffffffu, v, k);
-                if (lane < k) v = fma(-D[k][lane], xk, v);
+            if (N > A.bigN && !A.panel_v1) {
+                // x = inv(L11)' v: x_k = v_k + sum_{i > k} inv(L11)(i, k) v_i, inv(L11)(i, k) stored at (k, i)
+                double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+                for (int i = 0; i < nb; i += 4) {
+                    if (i > lane && i < nb) p0 = fma(D[lane][i], vec[kb + i], p0);
+                    if (i + 1 > lane && i + 1 < nb) p1 = fma(D[lane][i + 1], vec[kb + i + 1], p1);
+                    if (i + 2 > lane && i + 2 < nb) p2 = fma(D[lane][i + 2], vec[kb + i + 2], p2);
+                    if (i + 3 > lane && i + 3 < nb) p3 = fma(D[lane][i + 3], vec[kb + i + 3], p3);
+                }
+                __syncwarp();
+                v += (p0 + p1) + (p2 + p3);
+            } else {
+                for (int k = nb - 1; k >= 0; k--) {
+                    const double xk = __shfl_sync(0xffffffffu, v, k);
+                    if (lane < k) v = fma(-D[k][lane], xk, v);
+                }
             }
             if (lane < nb) { vec[kb + lane] = v; A.xs[f + kb + lane] = v; }
         }
@@ -594,6 +791,7 @@ static FArgs fargs(qpdo_dev *d)
     FArgs A;
     A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
     A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Up = F.Up; A.Lx = F.Lx; A.Ux = F.Ux; A.Xout = F.Xout; A.sc = d->sc;
+    A.fdesc = (const FrontDesc *)F.fdesc;
     return A;
 }
 static SArgs sargs(qpdo_dev *d)
@@ -601,7 +799,7 @@ static SArgs sargs(qpdo_dev *d)
     Factor &F = d->F;
     SArgs A;
     A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
-    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.Xout = F.Xout; A.bigN = BUCKET_N[3]; A.xs = F.xs; A.uv = F.uv;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.Xout = F.Xout; A.bigN = BUCKET_N[3]; A.panel_v1 = F.panel_v1 ? 1 : 0; A.xs = F.xs; A.uv = F.uv;
     return A;
 }
 
@@ -660,6 +858,8 @@ int factor_setup(qpdo_dev *d, int ordering)
     if (cudaMallocHost((void **)&F.cnt_host, 2 * sizeof(int)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); return -1; }
     cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(k_big_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PANEL_SMEM);
+    { const char *pv = getenv("QPDO_B200_PANEL"); F.panel_v1 = pv && !strcmp(pv, "v1"); }   // A/B against the round-1 panel step
     const char *ev = getenv("QPDO_PATTERN");              // "superset" | "dynamic" override the size rule (tests)
     F.dynamic = (m >= DYNAMIC_MIN_ROWS);
     if (ev && !strcmp(ev, "superset")) F.dynamic = false;
@@ -718,6 +918,13 @@ static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
         f_alloc(d, &F.Kt_val, S->ntriple) || f_alloc(d, &F.Lx, S->lnz_stored) || f_alloc(d, &F.Xout, S->max_front > BUCKET_N[3] ? S->lnz_stored : 1) || f_alloc(d, &F.Ux, S->usize) ||
         f_alloc(d, &F.uv, nrows))
         return -1;
+    {
+        std::vector<FrontDesc> fdh((size_t)ns);
+        for (int t = 0; t < ns; t++) { fdh[t].Lp = S->Lp[t]; fdh[t].Up = S->Up[t]; fdh[t].nc = S->sn_start[t + 1] - S->sn_start[t]; fdh[t].nr = S->sn_nr[t]; }
+        FrontDesc *fdd = nullptr;
+        if (f_upload(d, &fdd, (const FrontDesc *)fdh.data(), (size_t)ns)) return -1;
+        F.fdesc = fdd;
+    }
     // launch plan: per level, fronts are sorted by decreasing order N
     F.plan.assign(S->nlevel, std::vector<FrontLaunch>());
     for (int lv = 0; lv < S->nlevel; lv++) {
@@ -789,7 +996,19 @@ static long issue_factor(qpdo_dev *d)
                 k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, d->st>>>(A, list); launches++;
                 for (int kb = 0; kb < L.maxnc; kb += NB) {
                     const int R = L.maxN - kb - 1, nt = R > 0 ? cdiv(R, TS) : 0;
-                    k_big_panel<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, d->st>>>(A, list, kb); launches++;
+                    if (F.panel_v1) k_big_panel_v1<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, d->st>>>(A, list, kb);
+                    else {
+                        PanelFronts PF; PF.count = 0;
+                        if (L.count <= PANEL_PARAM_FRONTS) {        // few fronts: descriptors travel as kernel parameters
+                            PF.count = L.count;
+                            for (int t = 0; t < L.count; t++) {
+                                const int sn = S->level_sn[L.first + t];
+                                PF.d[t].Lp = S->Lp[sn]; PF.d[t].Up = S->Up[sn]; PF.d[t].nc = S->sn_start[sn + 1] - S->sn_start[sn]; PF.d[t].nr = S->sn_nr[sn];
+                            }
+                        }
+                        k_big_panel<<<dim3(L.count, 1 + nt * (nt + 1) / 2), 256, PANEL_SMEM, d->st>>>(A, list, kb, PF);
+                    }
+                    launches++;
                 }
             } else {
                 size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 8 * (size_t)L.maxN);
