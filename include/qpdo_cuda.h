@@ -130,6 +130,20 @@ int  qpdo_dev_test_linesearch(qpdo_dev *d, const double *dx, const double *Qdx, 
                               const double *Adx, const double *w, const double *l, const double *u,
                               double *tau);
 
+/* K x = b on the factorization that is in place, WITHOUT allocating: the supernodal triangular solves of
+ * qpdo_dev_test_factor_solve / the Newton step (k_fwd, k_bwd) with their scratch (right-hand side, permuted vector,
+ * solution, per-front update vectors: 3 n + front rows doubles) in one static device array of
+ * qpdo_dev_solve_noalloc_max_doubles() = 524,288 doubles (4 MiB per GPU, held until the library is unloaded).
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  b and x are host or device
+ * pointers of n doubles.  Calls no cudaMalloc / cudaFree / allocating routine and launches the kernels directly (no
+ * graph instantiation).  Returns 0; -2 with a message naming the limit when the problem needs more scratch than the
+ * array holds; -1 on other errors (no factorization yet, CUDA errors).  All calls on one GPU share the array, which
+ * keeps the last call's contents (cleared per call where a solve reads before writing): calls that overlap on
+ * the GPU race. */
+int  qpdo_dev_solve_noalloc(qpdo_dev *d, const double *b, double *x);
+long qpdo_dev_solve_noalloc_max_doubles(void);
+
 /* measured FP64 peaks of `device` (< 0: current), TFLOP/s: register-resident mma.sync.m8n8k4.f64 (DMMA) and DFMA
  * loops over all SMs, best of four timed launches.  The roofline denominators of the numeric factorization. */
 int  qpdo_dev_measure_fp64(int device, double *dmma_tflops, double *dfma_tflops);

@@ -354,6 +354,8 @@ def declare_device_layer(lib):
     lib.qpdo_dev_test_factor_solve.argtypes = [vp, _pd, C.c_double, _pd, _pd, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.qpdo_dev_test_spmv.argtypes = [vp, C.c_int, _pd, _pd]
     lib.qpdo_dev_measure_fp64.argtypes = [C.c_int, _pd, _pd]
+    lib.qpdo_dev_solve_noalloc.argtypes = [vp, _pd, _pd]
+    lib.qpdo_dev_solve_noalloc_max_doubles.restype = C.c_long
     return lib
 
 

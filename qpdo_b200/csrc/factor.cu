@@ -841,6 +841,7 @@ __global__ void k_support(const double *omega, const unsigned char *inP, int m, 
 }
 
 static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask);
+int factor_noalloc_setup(qpdo_dev *d);                 // address of the static scratch of qpdo_dev_solve_noalloc, once per device
 
 int factor_setup(qpdo_dev *d, int ordering)
 {
@@ -856,6 +857,7 @@ int factor_setup(qpdo_dev *d, int ordering)
     CUDA_OK(cudaStreamSynchronize(d->st));
     if (dev_alloc(d, &F.xs, n) || dev_alloc(d, &F.inP, (size_t)std::max(m, 1)) || dev_alloc(d, &F.cnt, 2)) return -1;
     if (cudaMallocHost((void **)&F.cnt_host, 2 * sizeof(int)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); return -1; }
+    if (factor_noalloc_setup(d)) return -1;
     cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(k_big_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PANEL_SMEM);
@@ -1020,11 +1022,10 @@ static long issue_factor(qpdo_dev *d)
         }
     return launches;
 }
-static long issue_solve(qpdo_dev *d)
+static long issue_solve_args(qpdo_dev *d, const SArgs &A)
 {
     Factor &F = d->F;
     const qpdo_symbolic *S = F.S;
-    SArgs A = sargs(d);
     long launches = 0;
     auto ordN = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s] + S->sn_nr[s]; };
     for (int pass = 0; pass < 2; pass++)
@@ -1059,6 +1060,7 @@ static long issue_solve(qpdo_dev *d)
         }
     return launches;
 }
+static long issue_solve(qpdo_dev *d) { return issue_solve_args(d, sargs(d)); }
 static int capture(qpdo_dev *d, long (*issue)(qpdo_dev *), cudaGraphExec_t *out, long *launches)
 {
     cudaGraph_t g = nullptr;
@@ -1109,4 +1111,69 @@ void factor_destroy(qpdo_dev *d)
     factor_release(d);
     if (F.cnt_host) cudaFreeHost(F.cnt_host);
     F.cnt_host = nullptr;
+}
+
+// =============================================================================== no-allocation solve
+// qpdo_dev_solve_noalloc: the supernodal triangular solves (k_fwd / k_bwd, the kernels of factor_solve) on the factor
+// that is in place, for callers that must not allocate (code under CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.  The scratch
+// of the solve -- the unpermuted right-hand side, the permuted vector xs, the unpermuted solution and the per-front
+// update vectors uv -- lives in ONE file-scope device array of QPDO_NOALLOC_MAX_DOUBLES doubles (4 MiB, held by every
+// GPU that loads the library until exit) instead of cudaMalloc'ed buffers; the kernels are launched directly (no
+// graph instantiation, which allocates).  Every call shares the array and finds the previous call's contents in
+// it: what a solve reads before writing (nothing but uv, cleared below for good measure) is cleared per call;
+// two calls that overlap on the GPU (different streams, different contexts of one device) race on it.
+#define QPDO_NOALLOC_MAX_DOUBLES (1 << 19)
+static __device__ __align__(256) double g_noalloc_scratch[QPDO_NOALLOC_MAX_DOUBLES];
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: its address is looked up once per
+// device, with that device current, and only the looked-up pointer is ever handed to a kernel or a copy.
+#define QPDO_NOALLOC_MAX_DEVICES 64
+static double *g_noalloc_addr[QPDO_NOALLOC_MAX_DEVICES];
+
+static int noalloc_scratch_lookup(int device, double **out)
+{
+    if (device < 0 || device >= QPDO_NOALLOC_MAX_DEVICES) { qpdo_set_error("qpdo_dev_solve_noalloc: device %d out of range", device); return -1; }
+    if (!g_noalloc_addr[device]) {
+        double *ptr = nullptr;
+        CUDA_OK(cudaSetDevice(device));
+        CUDA_OK(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+        if (!ptr) { qpdo_set_error("qpdo_dev_solve_noalloc: cudaGetSymbolAddress returned a null address"); return -1; }
+        g_noalloc_addr[device] = ptr;
+    }
+    if (out) *out = g_noalloc_addr[device];
+    return 0;
+}
+// set-up hook: called from factor_setup with the context's device current
+int factor_noalloc_setup(qpdo_dev *d) { return noalloc_scratch_lookup(d->device, nullptr); }
+
+extern "C" long qpdo_dev_solve_noalloc_max_doubles(void) { return (long)QPDO_NOALLOC_MAX_DOUBLES; }
+
+extern "C" int qpdo_dev_solve_noalloc(qpdo_dev *d, const double *b, double *x)
+{
+    if (!d || !b || !x) { qpdo_set_error("qpdo_dev_solve_noalloc: null argument"); return -1; }
+    CUDA_OK(cudaSetDevice(d->device));
+    Factor &F = d->F;
+    if (!F.S) { qpdo_set_error("qpdo_dev_solve_noalloc: no factorization in place (call after a Newton step or qpdo_dev_test_factor_solve)"); return -1; }
+    const qpdo_symbolic *S = F.S;
+    const size_t n = (size_t)d->n, nrows = (size_t)S->sn_rowptr[S->nsuper];
+    const size_t need = 3 * n + nrows;
+    if (need > (size_t)QPDO_NOALLOC_MAX_DOUBLES) {
+        qpdo_set_error("qpdo_dev_solve_noalloc: the solve needs %zu doubles of scratch (3 n + front rows, n = %zu), the static scratch holds %d (%d MiB); use the allocating path",
+                       need, n, QPDO_NOALLOC_MAX_DOUBLES, (int)(QPDO_NOALLOC_MAX_DOUBLES * sizeof(double) >> 20));
+        return -2;
+    }
+    double *base = nullptr;
+    if (noalloc_scratch_lookup(d->device, &base)) return -1;
+    double *rhs = base, *xs = base + n, *xout = base + 2 * n, *uv = base + 3 * n;
+    CUDA_OK(cudaMemsetAsync(uv, 0, sizeof(double) * (nrows ? nrows : 1), d->st));
+    CUDA_OK(cudaMemcpyAsync(rhs, b, sizeof(double) * n, cudaMemcpyDefault, d->st));
+    SArgs A = sargs(d);
+    A.xs = xs; A.uv = uv;
+    k_permute_in<<<cdiv(d->n, 256), 256, 0, d->st>>>(rhs, F.perm, xs, d->n);
+    issue_solve_args(d, A);
+    k_permute_out<<<cdiv(d->n, 256), 256, 0, d->st>>>(xs, F.perm, xout, d->n);
+    CUDA_OK(cudaGetLastError());
+    CUDA_OK(cudaMemcpyAsync(x, xout, sizeof(double) * n, cudaMemcpyDefault, d->st));
+    CUDA_OK(cudaStreamSynchronize(d->st));
+    return 0;
 }
