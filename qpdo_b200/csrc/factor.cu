@@ -66,10 +66,29 @@ __device__ __forceinline__ double div_by_pivot(double u, double d, double r)
 // ------------------------------------------------------------------------------- smem fronts
 // One CTA per front: load the panel, extend-add the children's update matrices in fixed order,
 // eliminate the nc pivot columns (right-looking), write the panel and the Schur complement.
+#ifdef FRONT_PROBE
+// -DFRONT_PROBE: per template (NT = 64 / 128 / 256) sums of the SM cycles a CTA spends in its phases (tools/probe_front.py)
+__device__ unsigned long long g_fprobe[3][12];
+#define FPROBE(i) do { if (threadIdx.x == 0) fp[i] = clock64(); } while (0)
+extern "C" int qpdo_dev_fprobe_read(unsigned long long *out)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_fprobe, sizeof(unsigned long long) * 36);
+    unsigned long long z[36] = {0};
+    cudaMemcpyToSymbol(g_fprobe, z, sizeof z);
+    return 0;
+}
+#else
+#define FPROBE(i)
+#endif
 template <int NT>
 __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
 {
     extern __shared__ double F[];
+#ifdef FRONT_PROBE
+    long long fp[6], fpanel = 0, ftrail = 0, fur = 0, ft0 = 0;
+#endif
+    FPROBE(0);
     const int s = list[blockIdx.x];
     const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr, ld = N | 1;
     double *Lp = A.Lx + A.Lp[s];
@@ -77,6 +96,7 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
     for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; F[i + j * ld] = Lp[idx]; }
     for (int idx = tid; idx < N * nr; idx += NT) { int j = idx / N, i = idx - j * N; F[i + (nc + j) * ld] = 0.0; }
     __syncthreads();
+    FPROBE(1);
     for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
         const int c = A.child_idx[t], rc = A.sn_nr[c];
         const int *rl = A.rel + A.sn_rowptr[c];
@@ -87,6 +107,7 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
         }
         __syncthreads();
     }
+    FPROBE(2);
     // right-looking LDL' in blocks of KB pivots.  Panel phase, per pivot: the rows below it compute
     // l_i = a_ik / d_k (unscaled u_i and scaled l_i go to the ub / lb buffers, the L entry is final), then the
     // remaining panel columns are updated.  Trailing phase, once per block: warp per column, lane per row
@@ -98,53 +119,110 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
     double *ub = F + (size_t)ld * N, *lb = ub + KB * N;
     for (int kb = 0; kb < nc; kb += KB) {
         const int nk = min(KB, nc - kb);
-        for (int t = 0; t < nk; t++) {
-            const int k = kb + t;
-            const double dk = F[k + k * ld];
-            if (tid == 0 && !(dk > 0.0)) A.sc->not_posdef = 1;
-            const double rk = __drcp_rn(dk);
-            for (int i = k + 1 + tid; i < N; i += NT) {
-                const double u = F[i + k * ld], l = div_by_pivot(u, dk, rk);
-                ub[t * N + i] = u; lb[t * N + i] = l; F[i + k * ld] = l;
+        // panel: one thread per row i >= kb with the row's KB panel entries in registers.  EVERY thread loads the
+        // KB x KB pivot block (broadcast loads) and factors it redundantly, so a thread finishes its own row with no
+        // exchange and no barrier on the pivot chain.  Per entry the operations are those of the column-by-column
+        // elimination (u / d by div_by_pivot, a_ic = fma(-u_i, l_c, a_ic) in ascending pivot order): same bits.
+#ifdef FRONT_PROBE
+        if (tid == 0) ft0 = clock64();
+#endif
+        for (int i = kb + tid; i < N; i += NT) {
+            double P[KB][KB], a[KB], u[KB], l[KB];
+#pragma unroll
+            for (int c = 0; c < KB; c++)
+#pragma unroll
+                for (int r = c; r < KB; r++) P[c][r] = (r < nk && c < nk) ? F[(kb + r) + (kb + c) * ld] : (r == c ? 1.0 : 0.0);
+#pragma unroll
+            for (int t = 0; t < KB; t++) a[t] = (t < nk) ? F[i + (kb + t) * ld] : 0.0;
+            bool bad = false;
+#pragma unroll
+            for (int t = 0; t < KB; t++) {
+                const double dt = P[t][t];
+                bad = bad || (t < nk && !(dt > 0.0));
+                const double rt = __drcp_rn(dt);
+                double L[KB];
+#pragma unroll
+                for (int r = t + 1; r < KB; r++) L[r] = div_by_pivot(P[t][r], dt, rt);
+#pragma unroll
+                for (int c = t + 1; c < KB; c++)
+#pragma unroll
+                    for (int r = c; r < KB; r++) P[c][r] = fma(-P[t][r], L[c], P[c][r]);
+                u[t] = a[t];
+                l[t] = div_by_pivot(a[t], dt, rt);
+#pragma unroll
+                for (int c = t + 1; c < KB; c++) a[c] = fma(-u[t], L[c], a[c]);
             }
-            __syncthreads();
-            if (t + 1 < nk) {
-                for (int c = k + 1; c < kb + nk; c++) {
-                    const double lc = lb[t * N + c];
-                    for (int i = c + tid; i < N; i += NT) F[i + c * ld] = fma(-ub[t * N + i], lc, F[i + c * ld]);
+            if (bad && i == kb) A.sc->not_posdef = 1;
+#pragma unroll
+            for (int t = 0; t < KB; t++) {
+                if (t < nk) {
+                    const int k = kb + t;
+                    if (i > k) { F[i + k * ld] = l[t]; ub[t * N + i] = u[t]; lb[t * N + i] = l[t]; }
+                    else if (i == k) F[i + k * ld] = u[t];          // the pivot itself, after the updates of this block
                 }
-                __syncthreads();
             }
         }
+        __syncthreads();
+#ifdef FRONT_PROBE
+        if (tid == 0) { const long long t1 = clock64(); fpanel += t1 - ft0; ft0 = t1; }
+#endif
         double ur[RMAX][KB];
 #pragma unroll
         for (int r = 0; r < RMAX; r++)
 #pragma unroll
             for (int t = 0; t < KB; t++) { const int i = lane + 32 * r; ur[r][t] = (t < nk && i < N) ? ub[t * N + i] : 0.0; }
-        for (int j = kb + nk + wid; j < N; j += NW) {
-            double lj[KB];
+#ifdef FRONT_PROBE
+        if (tid == 0) { const long long t1 = clock64(); fur += t1 - ft0; ft0 = t1; }
+#endif
+        // two columns per iteration, all loads before the first store (the compiler cannot reorder a load of F
+        // over a store to F): 2 x RMAX independent 4-fma chains in flight instead of one.  Pivots beyond nk have
+        // u = l = 0 and fma(-0, 0, v) == v, so no guard is needed.
+        for (int j0 = kb + nk + wid; j0 < N; j0 += 2 * NW) {
+            const int j1 = j0 + NW;
+            const bool two = j1 < N;
+            double l0[KB], l1[KB], v0[RMAX], v1[RMAX];
 #pragma unroll
-            for (int t = 0; t < KB; t++) lj[t] = (t < nk) ? lb[t * N + j] : 0.0;
+            for (int t = 0; t < KB; t++) { l0[t] = (t < nk) ? lb[t * N + j0] : 0.0; l1[t] = (t < nk && two) ? lb[t * N + j1] : 0.0; }
 #pragma unroll
             for (int r = 0; r < RMAX; r++) {
                 const int i = lane + 32 * r;
-                if (i >= j && i < N) {
-                    double v = F[i + j * ld];
+                v0[r] = (i >= j0 && i < N) ? F[i + j0 * ld] : 0.0;
+                v1[r] = (two && i >= j1 && i < N) ? F[i + j1 * ld] : 0.0;
+            }
 #pragma unroll
-                    for (int t = 0; t < KB; t++) if (t < nk) v = fma(-ur[r][t], lj[t], v);
-                    F[i + j * ld] = v;
-                }
+            for (int t = 0; t < KB; t++)
+#pragma unroll
+                for (int r = 0; r < RMAX; r++) { v0[r] = fma(-ur[r][t], l0[t], v0[r]); v1[r] = fma(-ur[r][t], l1[t], v1[r]); }
+#pragma unroll
+            for (int r = 0; r < RMAX; r++) {
+                const int i = lane + 32 * r;
+                if (i >= j0 && i < N) F[i + j0 * ld] = v0[r];
+                if (two && i >= j1 && i < N) F[i + j1 * ld] = v1[r];
             }
         }
         __syncthreads();
+#ifdef FRONT_PROBE
+        if (tid == 0) { const long long t1 = clock64(); ftrail += t1 - ft0; }
+#endif
     }
     __syncthreads();
+    FPROBE(3);
     for (int idx = tid; idx < N * nc; idx += NT) { int j = idx / N, i = idx - j * N; Lp[idx] = (i >= j) ? F[i + j * ld] : 0.0; }
     double *U = A.Ux + A.Up[s];
     for (int idx = tid; idx < nr * nr; idx += NT) {
         int j = idx / nr, i = idx - j * nr;
         if (i >= j) U[idx] = F[(nc + i) + (nc + j) * ld];
     }
+#ifdef FRONT_PROBE
+    FPROBE(4);
+    if (threadIdx.x == 0) {
+        const int w = NT == 64 ? 0 : (NT == 128 ? 1 : 2);
+        for (int i = 0; i < 4; i++) atomicAdd(&g_fprobe[w][i], (unsigned long long)(fp[i + 1] - fp[i]));
+        atomicAdd(&g_fprobe[w][4], 1ull); atomicAdd(&g_fprobe[w][5], (unsigned long long)N); atomicAdd(&g_fprobe[w][6], (unsigned long long)nc);
+        atomicAdd(&g_fprobe[w][7], (unsigned long long)(A.child_ptr[s + 1] - A.child_ptr[s]));
+        atomicAdd(&g_fprobe[w][8], (unsigned long long)fpanel); atomicAdd(&g_fprobe[w][9], (unsigned long long)fur); atomicAdd(&g_fprobe[w][10], (unsigned long long)ftrail);
+    }
+#endif
 }
 
 // ------------------------------------------------------------------------------- big fronts
