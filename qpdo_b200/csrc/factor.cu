@@ -126,14 +126,20 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
 #ifdef FRONT_PROBE
         if (tid == 0) ft0 = clock64();
 #endif
-        for (int i = kb + tid; i < N; i += NT) {
-            double P[KB][KB], a[KB], u[KB], l[KB];
+        // (NT >= N in every bucket: one row per thread.)  The pivot rows' threads overwrite the pivot block with their
+        // L entries, so every thread must have loaded the block before anyone stores: barrier between loads and stores.
+        const int i = kb + tid;
+        const bool act = i < N;
+        double P[KB][KB], a[KB];
 #pragma unroll
-            for (int c = 0; c < KB; c++)
+        for (int c = 0; c < KB; c++)
 #pragma unroll
-                for (int r = c; r < KB; r++) P[c][r] = (r < nk && c < nk) ? F[(kb + r) + (kb + c) * ld] : (r == c ? 1.0 : 0.0);
+            for (int r = c; r < KB; r++) P[c][r] = (r < nk && c < nk) ? F[(kb + r) + (kb + c) * ld] : (r == c ? 1.0 : 0.0);
 #pragma unroll
-            for (int t = 0; t < KB; t++) a[t] = (t < nk) ? F[i + (kb + t) * ld] : 0.0;
+        for (int t = 0; t < KB; t++) a[t] = (act && t < nk) ? F[i + (kb + t) * ld] : 0.0;
+        __syncthreads();
+        if (act) {
+            double u[KB], l[KB];
             bool bad = false;
 #pragma unroll
             for (int t = 0; t < KB; t++) {
@@ -936,6 +942,13 @@ int factor_setup(qpdo_dev *d, int ordering)
     if (dev_alloc(d, &F.xs, n) || dev_alloc(d, &F.inP, (size_t)std::max(m, 1)) || dev_alloc(d, &F.cnt, 2)) return -1;
     if (cudaMallocHost((void **)&F.cnt_host, 2 * sizeof(int)) != cudaSuccess) { qpdo_set_error("cudaMallocHost failed"); return -1; }
     if (factor_noalloc_setup(d)) return -1;
+    for (int b = 0; b < 4; b++) {
+        if (cudaStreamCreateWithFlags(&F.aux[b], cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&F.ev_join[b], cudaEventDisableTiming) != cudaSuccess) {
+            qpdo_set_error("factor_setup: stream / event creation failed"); return -1;
+        }
+    }
+    if (cudaEventCreateWithFlags(&F.ev_fork, cudaEventDisableTiming) != cudaSuccess) { qpdo_set_error("factor_setup: event creation failed"); return -1; }
+    { const char *cv = getenv("QPDO_B200_CONCURRENT"); F.concurrent = !(cv && !strcmp(cv, "0")); }
     cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(k_big_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PANEL_SMEM);
@@ -1063,20 +1076,41 @@ int factor_refresh_products(qpdo_dev *d)
     return 0;
 }
 
+// the launches of one level are independent of each other: branch b > 0 goes to its own stream (a parallel branch of
+// the captured graph), the level ends with a join on the main stream
+static void fork_level(qpdo_dev *d, int nbranch, cudaStream_t *sv)
+{
+    Factor &F = d->F;
+    for (int b = 0; b < nbranch; b++) sv[b] = d->st;
+    if (nbranch <= 1 || !F.concurrent) return;
+    cudaEventRecord(F.ev_fork, d->st);
+    for (int b = 1; b < nbranch && b <= 4; b++) { sv[b] = F.aux[b - 1]; cudaStreamWaitEvent(sv[b], F.ev_fork, 0); }
+}
+static void join_level(qpdo_dev *d, int nbranch, cudaStream_t *sv)
+{
+    Factor &F = d->F;
+    if (nbranch <= 1 || !F.concurrent) return;
+    for (int b = 1; b < nbranch && b <= 4; b++) { cudaEventRecord(F.ev_join[b - 1], sv[b]); cudaStreamWaitEvent(d->st, F.ev_join[b - 1], 0); }
+}
 static long issue_factor(qpdo_dev *d)
 {
     Factor &F = d->F;
     const qpdo_symbolic *S = F.S;
     FArgs A = fargs(d);
     long launches = 0;
-    for (int lv = 0; lv < S->nlevel; lv++)
+    for (int lv = 0; lv < S->nlevel; lv++) {
+        cudaStream_t sv[8];
+        const int nbranch = (int)F.plan[lv].size();
+        fork_level(d, nbranch, sv);
+        int br = 0;
         for (const FrontLaunch &L : F.plan[lv]) {
             const int *list = F.level_sn + L.first;
+            cudaStream_t st = sv[br++];
             if (L.kind == 2) {
-                k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, d->st>>>(A, list); launches++;
+                k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, st>>>(A, list); launches++;
                 for (int kb = 0; kb < L.maxnc; kb += NB) {
                     const int R = L.maxN - kb - 1, nt = R > 0 ? cdiv(R, TS) : 0;
-                    if (F.panel_v1) k_big_panel_v1<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, d->st>>>(A, list, kb);
+                    if (F.panel_v1) k_big_panel_v1<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, st>>>(A, list, kb);
                     else {
                         PanelFronts PF; PF.count = 0;
                         if (L.count <= PANEL_PARAM_FRONTS) {        // few fronts: descriptors travel as kernel parameters
@@ -1086,18 +1120,20 @@ static long issue_factor(qpdo_dev *d)
                                 PF.d[t].Lp = S->Lp[sn]; PF.d[t].Up = S->Up[sn]; PF.d[t].nc = S->sn_start[sn + 1] - S->sn_start[sn]; PF.d[t].nr = S->sn_nr[sn];
                             }
                         }
-                        k_big_panel<<<dim3(L.count, 1 + nt * (nt + 1) / 2), 256, PANEL_SMEM, d->st>>>(A, list, kb, PF);
+                        k_big_panel<<<dim3(L.count, 1 + nt * (nt + 1) / 2), 256, PANEL_SMEM, st>>>(A, list, kb, PF);
                     }
                     launches++;
                 }
             } else {
                 size_t smem = sizeof(double) * ((size_t)(L.maxN | 1) * L.maxN + 8 * (size_t)L.maxN);
-                if (L.maxnc == 0) k_front_smem<64><<<L.count, 64, smem, d->st>>>(A, list);
-                else if (L.maxnc == 1) k_front_smem<128><<<L.count, 128, smem, d->st>>>(A, list);
-                else k_front_smem<256><<<L.count, 256, smem, d->st>>>(A, list);
+                if (L.maxnc == 0) k_front_smem<64><<<L.count, 64, smem, st>>>(A, list);
+                else if (L.maxnc == 1) k_front_smem<128><<<L.count, 128, smem, st>>>(A, list);
+                else k_front_smem<256><<<L.count, 256, smem, st>>>(A, list);
                 launches++;
             }
         }
+        join_level(d, nbranch, sv);
+    }
     return launches;
 }
 static long issue_solve_args(qpdo_dev *d, const SArgs &A)
@@ -1111,30 +1147,37 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
             int lv = pass == 0 ? t : S->nlevel - 1 - t;
             int b = S->level_ptr[lv], e = S->level_ptr[lv + 1], q = b;
             while (q < e && ordN(q) > SOLVE_WARP_N) q++;
-            if (q > b) {
+            // fronts wider than SOLVE_BIG_N rows get 1024 threads (one panel row / one panel column per
+            // thread / warp), the rest of the CTA-solved fronts 256, fronts up to SOLVE_WARP_N one warp: up to three
+            // independent launches per level, each on its own branch
+            int qb = b;
+            while (qb < q && ordN(qb) > SOLVE_BIG_N) qb++;
+            const int nbranch = (qb > b) + (q > qb) + (e > q);
+            cudaStream_t sv[4];
+            fork_level(d, nbranch, sv);
+            int br = 0;
+            if (qb > b) {
+                cudaStream_t st = sv[br++];
                 size_t smem = sizeof(double) * (ordN(b) + NB);
-                // fronts wider than SOLVE_BIG_N rows get 1024 threads (one panel row / one panel column per
-                // thread / warp), the rest of the CTA-solved fronts 256
-                int qb = b;
-                while (qb < q && ordN(qb) > SOLVE_BIG_N) qb++;
-                if (qb > b) {
-                    if (pass == 0) k_fwd<1024><<<qb - b, 1024, smem, d->st>>>(A, F.level_sn + b);
-                    else k_bwd<1024><<<qb - b, 1024, smem, d->st>>>(A, F.level_sn + b);
-                    launches++;
-                }
-                if (q > qb) {
-                    smem = sizeof(double) * (ordN(qb) + NB);
-                    if (pass == 0) k_fwd<256><<<q - qb, 256, smem, d->st>>>(A, F.level_sn + qb);
-                    else k_bwd<256><<<q - qb, 256, smem, d->st>>>(A, F.level_sn + qb);
-                    launches++;
-                }
-            }
-            if (e > q) {
-                size_t smem = sizeof(double) * (ordN(q) + NB);
-                if (pass == 0) k_fwd<32><<<e - q, 32, smem, d->st>>>(A, F.level_sn + q);
-                else k_bwd<32><<<e - q, 32, smem, d->st>>>(A, F.level_sn + q);
+                if (pass == 0) k_fwd<1024><<<qb - b, 1024, smem, st>>>(A, F.level_sn + b);
+                else k_bwd<1024><<<qb - b, 1024, smem, st>>>(A, F.level_sn + b);
                 launches++;
             }
+            if (q > qb) {
+                cudaStream_t st = sv[br++];
+                size_t smem = sizeof(double) * (ordN(qb) + NB);
+                if (pass == 0) k_fwd<256><<<q - qb, 256, smem, st>>>(A, F.level_sn + qb);
+                else k_bwd<256><<<q - qb, 256, smem, st>>>(A, F.level_sn + qb);
+                launches++;
+            }
+            if (e > q) {
+                cudaStream_t st = sv[br++];
+                size_t smem = sizeof(double) * (ordN(q) + NB);
+                if (pass == 0) k_fwd<32><<<e - q, 32, smem, st>>>(A, F.level_sn + q);
+                else k_bwd<32><<<e - q, 32, smem, st>>>(A, F.level_sn + q);
+                launches++;
+            }
+            join_level(d, nbranch, sv);
         }
     return launches;
 }
@@ -1189,6 +1232,13 @@ void factor_destroy(qpdo_dev *d)
     factor_release(d);
     if (F.cnt_host) cudaFreeHost(F.cnt_host);
     F.cnt_host = nullptr;
+    for (int b = 0; b < 4; b++) {
+        if (F.aux[b]) cudaStreamDestroy(F.aux[b]);
+        if (F.ev_join[b]) cudaEventDestroy(F.ev_join[b]);
+        F.aux[b] = nullptr; F.ev_join[b] = nullptr;
+    }
+    if (F.ev_fork) cudaEventDestroy(F.ev_fork);
+    F.ev_fork = nullptr;
 }
 
 // =============================================================================== no-allocation solve

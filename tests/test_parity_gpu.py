@@ -177,6 +177,33 @@ def test_factor_solve_residual(cuda_lib, gen):
     s.delete()
 
 
+def test_factor_solve_is_deterministic_across_repeats_and_stream_modes(cuda_lib, monkeypatch):
+    """The same factorization + solve, 12 times over, and once more with the independent launches of a tree level on ONE
+    stream (QPDO_B200_CONCURRENT=0): every x bit-identical.  A race between warps of a front kernel or between the
+    concurrent branches of the captured graphs shows up here as a differing bit."""
+    import qpdo_b200
+    p = problems.cont_like(100)                   # 1,013 fronts: every size bucket and the blocked path
+    rng = np.random.default_rng(7)
+    xs = []
+    for mode in ("1", "0"):
+        monkeypatch.setenv("QPDO_B200_CONCURRENT", mode)
+        s = qpdo_b200.QPDO()
+        s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+        n, m = s.n, s.m
+        if not xs:
+            om = rng.random(m) * (rng.random(m) < 0.5) * 10
+            b = rng.standard_normal(n)
+        f, t = C.c_float(), C.c_float()
+        for rep in range(12 if mode == "1" else 2):
+            x = np.zeros(n)
+            assert cuda_lib.qpdo_dev_test_factor_solve(s.device, om.ctypes.data_as(_pd), 1e-3, b.ctypes.data_as(_pd), x.ctypes.data_as(_pd),
+                                                       C.byref(f), C.byref(t)) == 0, cuda_lib.qpdo_dev_last_error()
+            xs.append(x)
+        s.delete()
+    for x in xs[1:]:
+        assert np.array_equal(x, xs[0])
+
+
 def test_full_size_cont300_against_reference_golden(cuda_lib):
     """BASELINE config 3 at full size (n = 90,300, m = 180,300) against the unmodified reference's
     result (tests/golden/cont300.npz, make_golden_large.py) + KKT conditions recomputed on the host."""
