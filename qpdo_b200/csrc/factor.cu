@@ -18,7 +18,9 @@
 #include <string.h>
 
 #define NB 32          // panel width of the blocked path
-#define CW 32          // destination-column chunk of the big-front assembly
+#ifndef CW
+#define CW 8           // destination-column chunk of the big-front assembly: one column per warp
+#endif
 #define TS 64          // SYRK tile
 #define PLD 36         // padded leading dimension of a 64 x 32 panel tile in smem (conflict free)
 
@@ -434,7 +436,16 @@ __global__ void __launch_bounds__(256) k_big_panel_v1(FArgs A, const int *list, 
 //    in blocked fronts) -- and leaves; the tile pairs start at y == 1.
 #define TSP 68         // leading dimension of a k-major 32 x 64 tile (68 mod 16 == 4)
 #define LDI 36         // leading dimension of the k-major inverse (36 mod 16 == 4)
-#define PANEL_SMEM ((2 * NB * TSP + NB * NB + NB * LDI + NB + NB) * sizeof(double))
+#ifndef PANEL_SEQ
+#define PANEL_SEQ 0    // 0: inverse one step behind the LDL' (mbarrier per pivot column); 1: after it (named barrier), measured slower
+#endif
+#ifndef LGI
+#define LGI 32         // the same for the inverse warp's loop
+#endif
+#ifndef LG
+#define LG 32          // pivots per pass of the diagonal-block loops (32 = fully unrolled; -DLG=8 / 16 roll them, measured slower)
+#endif
+#define PANEL_SMEM ((2 * NB * TSP + NB * NB + NB + NB * LDI + NB + NB) * sizeof(double))
 #define PANEL_PARAM_FRONTS 16
 struct PanelFronts { int count; FrontDesc d[PANEL_PARAM_FRONTS]; };
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -492,7 +503,7 @@ extern "C" int qpdo_dev_probe_read(long long *out, int cap)
 __global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int kb, const __grid_constant__ PanelFronts PF)
 {
     extern __shared__ __align__(16) double psm[];
-    double *Ta = psm, *Tb = Ta + NB * TSP, *Us = Tb + NB * TSP, *LiT = Us + NB * NB, *Rinv = LiT + NB * LDI;
+    double *Ta = psm, *Tb = Ta + NB * TSP, *Us = Tb + NB * TSP, *LiT = Us + NB * NB + NB, *Rinv = LiT + NB * LDI;
     unsigned long long *bars = (unsigned long long *)(Rinv + NB);
 #ifdef PANEL_PROBE
     const bool probe_on = blockIdx.x == 0 && blockIdx.y == 1 && (threadIdx.x & 31) == 0;
@@ -565,68 +576,107 @@ __global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int
         }
         Us[lane] = a[0];
         __syncwarp();
+#if !PANEL_SEQ
         mbar_arrive_lane0(bars, lane);
+#endif
         double dk = Us[0];
         double r = rcp_pivot(dk);
         if (tid == 0) PROBE(4);
         bool bad = false;
+        // NB / LG passes of an LG-step unrolled body over a register WINDOW of the 32 columns: after a pass the LG
+        // finished columns leave the window (the writer CTA stores them) and the rest moves down.  Tried because the
+        // fully unrolled chain is ~25 KB of straight-line code that runs once per launch; measured, rolling does NOT
+        // pay (C3 factor 1.84 / 1.94 / 2.04 ms for LG = 32 / 16 / 8; a second pass over warm code in the same launch is no
+        // faster than the first), so LG = NB: one pass.  Window slot w = column kg + w.  NB: the -DPANEL_PROBE stamps
+        // themselves slow this chain by ~2x (15.7k cycles probed, ~7k by ncu sampling of the plain build).
+#pragma unroll 1
+        for (int kg = 0; kg < NB; kg += LG) {
 #pragma unroll
-        for (int k = 0; k < NB; k++) {
-            const double *uk = Us + k * NB;
-            bad = bad || (k < nb && !(dk > 0.0));
-            const double li = a[k] * r;
-            double dn = 1.0, rn = 1.0;
-            if (lane == k) Rinv[k] = r;
-            if (k + 1 < NB) {                                   // next pivot column first: published, its reciprocal started
-                a[k + 1] = fma(-li, uk[k + 1], a[k + 1]);
-                Us[(k + 1) * NB + lane] = a[k + 1];
-                __syncwarp();
-                mbar_arrive_lane0(bars + k + 1, lane);
-                dn = Us[(k + 1) * NB + k + 1];
-                rn = rcp_pivot(dn);
+            for (int t = 0; t < LG; t++) {
+                const int k = kg + t;
+                const double *uk = Us + k * NB + kg;            // uk[w]: entry (kg + w, k) of the block
+                bad = bad || (k < nb && !(dk > 0.0));
+                const double li = a[t] * r;
+                double dn = 1.0, rn = 1.0;
+                if (lane == k) Rinv[k] = r;
+                if (k + 1 < NB) {                               // next pivot column first: published, its reciprocal started
+                    a[t + 1] = fma(-li, uk[t + 1], a[t + 1]);
+                    Us[(k + 1) * NB + lane] = a[t + 1];
+                    __syncwarp();
+#if !PANEL_SEQ
+                    mbar_arrive_lane0(bars + k + 1, lane);
+#endif
+                    dn = Us[(k + 1) * NB + k + 1];
+                    rn = rcp_pivot(dn);
+                }
+                // the rest of the update is independent of the next reciprocal: the scheduler interleaves the two
+                // (slots beyond column 31 read the padding behind Us and are never used)
+                double u[NB];
+#pragma unroll
+                for (int j = ((t + 2) & ~1); j < NB; j += 2) { const double2 tt = *reinterpret_cast<const double2 *>(uk + j); u[j] = tt.x; u[j + 1] = tt.y; }
+#pragma unroll
+                for (int j = t + 2; j < NB; j++) a[j] = fma(-li, u[j], a[j]);
+                if (lane > k) a[t] = li;
+                dk = dn; r = rn;
             }
-            // the rest of the update is independent of the next reciprocal: the scheduler interleaves the two
-            double u[NB];
+            if (writer) {
 #pragma unroll
-            for (int j = ((k + 2) & ~1); j < NB; j += 2) { const double2 t = *reinterpret_cast<const double2 *>(uk + j); u[j] = t.x; u[j + 1] = t.y; }
+                for (int t = 0; t < LG; t++)
+                    if (kg + t < nb && lane < nb && lane >= kg + t) Xo[(int64_t)(kg + t) * N + kb + lane] = a[t];
+            }
 #pragma unroll
-            for (int j = k + 2; j < NB; j++) a[j] = fma(-li, u[j], a[j]);
-            if (lane > k) a[k] = li;
-            dk = dn; r = rn;
+            for (int w = 0; w + LG < NB; w++) a[w] = a[w + LG];
+#pragma unroll
+            for (int w = NB - LG; w < NB; w++) a[w] = 0.0;
         }
+#if PANEL_SEQ
+        asm volatile("bar.arrive 1, 64;" ::: "memory");       // releases the inverse warp (named barrier 1: warps 0 and 1)
+#endif
         if (tid == 0) PROBE(5);
-        if (writer) {
-            if (bad && lane == 0) A.sc->not_posdef = 1;
-#pragma unroll
-            for (int j = 0; j < NB; j++)
-                if (j < nb && lane < nb && lane >= j) Xo[(int64_t)j * N + kb + lane] = a[j];
-        }
+        if (writer && bad && lane == 0) A.sc->not_posdef = 1;
     } else if (wid == 1) {
         // ---- inv(L11), lane = column c: v[i] = inv(L11)(i, c); right-looking over the pivot columns as they appear
         // (step k uses column k and 1 / d_k, both published before the arrival on barrier k + 1)
+        // rolled like the LDL': window slot w holds row kg + w of column `lane` of the inverse; a row is final once the
+        // steps k < row are done, so the first 8 rows of the window leave it after every pass
         double v[NB];
 #pragma unroll
         for (int i = 0; i < NB; i++) v[i] = (i == lane) ? 1.0 : 0.0;
+#if PANEL_SEQ
+        asm volatile("bar.sync 1, 64;" ::: "memory");         // blocks in hardware until the LDL' warp is through
+#endif
+#pragma unroll 1
+        for (int kg = 0; kg < NB; kg += LGI) {
 #pragma unroll
-        for (int k = 0; k + 1 < NB; k++) {
-            mbar_wait(bars + k + 1, 0);
-            const double *uk = Us + k * NB;
-            double u[NB];
+            for (int t = 0; t < LGI; t++) {
+                const int k = kg + t;
+                if (k + 1 < NB) {
+#if !PANEL_SEQ
+                    mbar_wait(bars + k + 1, 0);
+#endif
+                    const double *uk = Us + k * NB + kg;
+                    double u[NB];
 #pragma unroll
-            for (int j = ((k + 1) & ~1); j < NB; j += 2) { const double2 t = *reinterpret_cast<const double2 *>(uk + j); u[j] = t.x; u[j + 1] = t.y; }
-            const double sk = Rinv[k] * v[k];
+                    for (int j = ((t + 1) & ~1); j < NB; j += 2) { const double2 tt = *reinterpret_cast<const double2 *>(uk + j); u[j] = tt.x; u[j + 1] = tt.y; }
+                    const double sk = Rinv[k] * v[t];
 #pragma unroll
-            for (int i = k + 1; i < NB; i++) v[i] = fma(-u[i], sk, v[i]);
+                    for (int i = t + 1; i < NB; i++) v[i] = fma(-u[i], sk, v[i]);
+                }
+            }
+            if (writer) {
+#pragma unroll
+                for (int t = 0; t < LGI; t++)
+                    if (kg + t >= 1 && kg + t < nb && lane < kg + t) Xo[(int64_t)(kg + t) * N + kb + lane] = v[t];
+            } else {
+#pragma unroll
+                for (int t = 0; t < LGI; t += 2) *reinterpret_cast<double2 *>(LiT + lane * LDI + kg + t) = make_double2(v[t], v[t + 1]);
+            }
+#pragma unroll
+            for (int w = 0; w + LGI < NB; w++) v[w] = v[w + LGI];
+#pragma unroll
+            for (int w = NB - LGI; w < NB; w++) v[w] = 0.0;
         }
         if (tid == 32) PROBE(6);
-        if (writer) {
-#pragma unroll
-            for (int i = 1; i < NB; i++)
-                if (i < nb && lane < i) Xo[(int64_t)i * N + kb + lane] = v[i];
-        } else {
-#pragma unroll
-            for (int i = 0; i < NB; i += 2) *reinterpret_cast<double2 *>(LiT + lane * LDI + i) = make_double2(v[i], v[i + 1]);
-        }
     } else if (!writer) {
         // ---- warps 2..7 stage the raw row tiles (k-major) by cp.async while the diagonal block is factored
         const int t192 = tid - 64;
