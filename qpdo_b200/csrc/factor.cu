@@ -12,10 +12,13 @@
 // panel loop (LDL' 32x32 -> trsm -> rank-32 SYRK on the FP64 tensor pipe, mma.sync m8n8k4 DMMA).
 // The whole sequence is captured once into a CUDA graph and replayed every Newton step.
 #include "dev_internal.h"
+#include <cooperative_groups.h>
 #include <algorithm>
 #include <chrono>
 #include <stdlib.h>
 #include <string.h>
+
+namespace cg = cooperative_groups;
 
 #define NB 32          // panel width of the blocked path
 #ifndef CW
@@ -454,6 +457,8 @@ __device__ __forceinline__ void cp_async8(double *dst_smem, const double *src)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" :: "r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N_> __device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;\n" :: "n"(N_) : "memory"); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" :: "r"(smem_u32(bar)), "r"(count) : "memory");
@@ -903,6 +908,175 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
         __syncthreads();
     }
 }
+
+// ---- cluster solves of the big fronts ----------------------------------------------------------------------
+// Fronts wider than SOLVE_BIG_N rows sit at the top of the tree, a handful per level, and their solves are a chain of
+// 32-column steps; one CTA per front keeps one SM's worth of loads in flight (~64 KB) and pays every L2 round trip of
+// a step in sequence.  Here a thread-block CLUSTER of SC CTAs solves one front: forward, the rows are dealt to the
+// CTAs in tiles of 32 (tile t -> CTA t mod SC); the CTA that owns the rows of the current diagonal block applies
+// inv(L11) (stored by k_big_panel), writes the block solution into every CTA's shared memory (distributed shared
+// memory), one cluster barrier, every CTA updates its own rows.  Backward, the 32 columns of a block are dealt to the
+// 32 warps of the cluster (the right-hand side is replicated), every warp sends its column sum to all CTAs, one
+// cluster barrier, every CTA applies inv(L11)' redundantly.  Per entry the operations and their order are those of
+// k_fwd / k_bwd: same bits.
+#define SC 8           // CTAs per cluster
+#define ST 128         // threads per CTA
+__global__ void __cluster_dims__(SC, 1, 1) __launch_bounds__(ST) k_fwd_cl(SArgs A, const int *list)
+{
+    cg::cluster_group cl = cg::this_cluster();
+    const int c = (int)cl.block_rank();
+    extern __shared__ double own[];                    // this CTA's rows: local tile lt = tile / SC, entry lt * 32 + (i & 31)
+    __shared__ double D[NB][NB + 1];
+    __shared__ double ybuf[2][NB];
+    const int s = list[blockIdx.x / SC];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    const double *L = A.Xout + A.Lp[s];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NW = ST / 32;
+    const int ntile = (N + 31) >> 5;
+    const int nown = ntile > c ? (ntile - c + SC - 1) / SC : 0;
+    for (int lt = wid; lt < nown; lt += NW) { const int i = ((lt * SC + c) << 5) + lane; own[lt * 32 + lane] = (i < nc) ? A.xs[f + i] : 0.0; }
+    __syncthreads();
+    for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
+        const int ch = A.child_idx[t], rc = A.sn_nr[ch];
+        const int *rl = A.rel + A.sn_rowptr[ch];
+        const double *u = A.uv + A.sn_rowptr[ch];
+        for (int idx = tid; idx < rc; idx += ST) {
+            const int r = rl[idx];
+            if (((r >> 5) % SC) == c) own[((r >> 5) / SC) * 32 + (r & 31)] += u[idx];
+        }
+        __syncthreads();
+    }
+    const int nblk = (nc + NB - 1) / NB;
+    double *stage = own + (nown + 1) * 32;             // [NB][ST]: panel entries of the next step for this thread's first row tile
+    auto prefetchD = [&](int b) {                      // diagonal block b (with inv(L11) in its upper triangle) into D
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        for (int idx = tid; idx < nb * nb; idx += ST) { const int j = idx / nb, i = idx - j * nb; cp_async8(&D[i][j], L + (int64_t)(kb + j) * N + kb + i); }
+    };
+    // the loads of a step do not depend on its data: they are issued as cp.async one step ahead (registers would not do:
+    // ptxas pairs every load with its fma, and the waiting fma then holds back the loads behind it)
+    const int i0 = ((wid * SC + c) << 5) + lane;       // row of this thread's first tile (lt = wid)
+    auto prefetchL = [&](int b) {
+        if (b < nblk) {
+            const int kb = b * NB, nb = min(NB, nc - kb);
+            if (wid < nown && i0 >= kb + nb && i0 < N)
+                for (int k = 0; k < nb; k++) cp_async8(stage + k * ST + tid, L + (int64_t)(kb + k) * N + i0);
+        }
+        cp_async_commit();
+    };
+    if (c < nblk) prefetchD(c);
+    cp_async_commit();
+    prefetchL(0);
+    for (int b = 0; b < nblk; b++) {
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        // groups in flight here: ..., D (older), L(b) (newest).  Every CTA commits the same sequence of groups.
+        if (c == b % SC) {                             // this CTA owns rows kb .. kb + 31
+            cp_async_wait_group<1>();
+            __syncthreads();                           // D landed; the other warps' updates of these rows are visible
+            if (wid == 0) {
+                const double *tb = own + (b / SC) * 32;
+                double v = (lane < nb) ? tb[lane] : 0.0;
+                double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+                for (int k = 0; k < nb; k += 4) {
+                    if (k < lane) p0 = fma(D[k][lane], tb[k], p0);
+                    if (k + 1 < lane) p1 = fma(D[k + 1][lane], tb[k + 1], p1);
+                    if (k + 2 < lane) p2 = fma(D[k + 2][lane], tb[k + 2], p2);
+                    if (k + 3 < lane) p3 = fma(D[k + 3][lane], tb[k + 3], p3);
+                }
+                v += (p0 + p1) + (p2 + p3);
+                for (int r = 0; r < SC; r++) cl.map_shared_rank(&ybuf[b & 1][0], r)[lane] = (lane < nb) ? v : 0.0;
+                if (lane < nb) A.xs[f + kb + lane] = v / D[lane][lane];
+            }
+            __syncthreads();                           // D is free again
+            if (b + SC < nblk) prefetchD(b + SC);
+        }
+        cp_async_commit();                             // the D group of this step (empty unless this CTA just prefetched)
+        cl.sync();
+        cp_async_wait_group<1>();                      // L(b) landed (each thread reads only what it copied itself)
+        const double *yb = ybuf[b & 1];
+        for (int lt = wid; lt < nown; lt += NW) {
+            const int i = ((lt * SC + c) << 5) + lane;
+            if (i >= kb + nb && i < N) {
+                double acc = 0.0;
+                if (lt == wid) {
+                    for (int k = 0; k < nb; k++) acc = fma(stage[k * ST + tid], yb[k], acc);
+                } else {                               // fronts beyond SC * ST rows: further tiles straight from global memory
+                    const double *Li = L + (int64_t)kb * N + i;
+                    for (int k = 0; k < nb; k++) acc = fma(Li[(int64_t)k * N], yb[k], acc);
+                }
+                own[lt * 32 + lane] -= acc;
+            }
+        }
+        prefetchL(b + 1);
+    }
+    double *u = A.uv + A.sn_rowptr[s];
+    for (int lt = wid; lt < nown; lt += NW) { const int i = ((lt * SC + c) << 5) + lane; if (i >= nc && i < N) u[i - nc] = own[lt * 32 + lane]; }
+    cl.sync();                                         // no CTA leaves while a peer may still write into its shared memory
+}
+__global__ void __cluster_dims__(SC, 1, 1) __launch_bounds__(ST) k_bwd_cl(SArgs A, const int *list)
+{
+    cg::cluster_group cl = cg::this_cluster();
+    const int c = (int)cl.block_rank();
+    extern __shared__ double vec[];                    // the front's N values, replicated in every CTA
+    __shared__ double Dd[2][NB][NB + 1];
+    __shared__ double tbuf[2][NB];
+    const int s = list[blockIdx.x / SC];
+    const int f = A.sn_start[s], nc = A.sn_start[s + 1] - f, nr = A.sn_nr[s], N = nc + nr;
+    const double *L = A.Xout + A.Lp[s];
+    const int *rows = A.rows + A.sn_rowptr[s];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int g = c * (ST / 32) + wid;                 // warp number in the cluster = column of the block it sums
+    for (int i = tid; i < N; i += ST) vec[i] = (i < nc) ? A.xs[f + i] : A.xs[rows[i - nc]];
+    const int nblk = (nc + NB - 1) / NB;
+    double *stage = vec + N + (N & 1) + wid * (size_t)(N + (N & 1));   // this warp's column of the next step (rows below the block)
+    auto prefetchD = [&](int b) {
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        double (*D)[NB + 1] = Dd[b & 1];
+        for (int idx = tid; idx < nb * nb; idx += ST) { const int j = idx / nb, i = idx - j * nb; cp_async8(&D[i][j], L + (int64_t)(kb + j) * N + kb + i); }
+    };
+    auto prefetchL = [&](int b) {                      // column kb + g, rows kb + nb .. N - 1, as cp.async (see k_fwd_cl)
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        if (g < nb) {
+            const double *Lk = L + (int64_t)(kb + g) * N;
+            for (int i = kb + nb + lane; i < N; i += 32) cp_async8(stage + i, Lk + i);
+        }
+    };
+    prefetchD(nblk - 1);
+    prefetchL(nblk - 1);
+    __syncthreads();
+    for (int b = nblk - 1; b >= 0; b--) {
+        const int kb = b * NB, nb = min(NB, nc - kb);
+        cp_async_wait_all();                           // this thread's part of D(b) and of its column; the cluster barrier below publishes D
+        if (b > 0) prefetchD(b - 1);
+        // t_k = vec[kb + k] - sum_{i >= kb + nb} L[i, kb + k] vec[i]: one warp of the cluster per column
+        if (g < nb) {
+            double acc = 0.0;
+            for (int i = kb + nb + lane; i < N; i += 32) acc = fma(stage[i], vec[i], acc);
+            for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            const double tk = vec[kb + g] - acc;
+            if (lane < SC) cl.map_shared_rank(&tbuf[b & 1][0], lane)[g] = tk;
+        }
+        __syncwarp();
+        if (b > 0) prefetchL(b - 1);                   // lands behind the barrier and the block solve
+        cl.sync();
+        if (wid == 0) {                                // every CTA applies inv(L11)' redundantly
+            const double (*D)[NB + 1] = Dd[b & 1];
+            const double *tb = tbuf[b & 1];
+            double v = (lane < nb) ? tb[lane] : 0.0;
+            double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+            for (int i = 0; i < nb; i += 4) {
+                if (i > lane && i < nb) p0 = fma(D[lane][i], tb[i], p0);
+                if (i + 1 > lane && i + 1 < nb) p1 = fma(D[lane][i + 1], tb[i + 1], p1);
+                if (i + 2 > lane && i + 2 < nb) p2 = fma(D[lane][i + 2], tb[i + 2], p2);
+                if (i + 3 > lane && i + 3 < nb) p3 = fma(D[lane][i + 3], tb[i + 3], p3);
+            }
+            v += (p0 + p1) + (p2 + p3);
+            if (lane < nb) { vec[kb + lane] = v; if (c == 0) A.xs[f + kb + lane] = v; }
+        }
+        __syncthreads();                               // x of this block visible to the CTA's warps
+    }
+    cl.sync();
+}
+
 __global__ void k_permute_in(const double *rhs, const int *perm, double *xs, int n)
 {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -999,6 +1173,9 @@ int factor_setup(qpdo_dev *d, int ordering)
     }
     if (cudaEventCreateWithFlags(&F.ev_fork, cudaEventDisableTiming) != cudaSuccess) { qpdo_set_error("factor_setup: event creation failed"); return -1; }
     { const char *cv = getenv("QPDO_B200_CONCURRENT"); F.concurrent = !(cv && !strcmp(cv, "0")); }
+    { const char *sv = getenv("QPDO_B200_SOLVE"); F.solve_cluster = !(sv && !strcmp(sv, "cta")); }   // "cta": one CTA per big front (A/B)
+    cudaFuncSetAttribute(k_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(k_big_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PANEL_SMEM);
@@ -1209,7 +1386,11 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
             if (qb > b) {
                 cudaStream_t st = sv[br++];
                 size_t smem = sizeof(double) * (ordN(b) + NB);
-                if (pass == 0) k_fwd<1024><<<qb - b, 1024, smem, st>>>(A, F.level_sn + b);
+                if (F.solve_cluster && !F.panel_v1 && ordN(b) <= 4096) {      // (shared-memory budget of k_bwd_cl: 5 N doubles)
+                    const int Nmax = ordN(b);
+                    if (pass == 0) k_fwd_cl<<<(qb - b) * SC, ST, sizeof(double) * (32 * (size_t)(cdiv(cdiv(Nmax, 32), SC) + 2) + NB * ST), st>>>(A, F.level_sn + b);
+                    else k_bwd_cl<<<(qb - b) * SC, ST, sizeof(double) * (size_t)(Nmax + 2) * (1 + ST / 32), st>>>(A, F.level_sn + b);
+                } else if (pass == 0) k_fwd<1024><<<qb - b, 1024, smem, st>>>(A, F.level_sn + b);
                 else k_bwd<1024><<<qb - b, 1024, smem, st>>>(A, F.level_sn + b);
                 launches++;
             }

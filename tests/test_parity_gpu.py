@@ -179,14 +179,15 @@ def test_factor_solve_residual(cuda_lib, gen):
 
 def test_factor_solve_is_deterministic_across_repeats_and_stream_modes(cuda_lib, monkeypatch):
     """The same factorization + solve, 12 times over, and once more with the independent launches of a tree level on ONE
-    stream (QPDO_B200_CONCURRENT=0): every x bit-identical.  A race between warps of a front kernel or between the
+    stream (QPDO_B200_CONCURRENT=0), and with the one-CTA solves of the big fronts (QPDO_B200_SOLVE=cta): every x bit-identical.  A race between warps of a front kernel or between the
     concurrent branches of the captured graphs shows up here as a differing bit."""
     import qpdo_b200
     p = problems.cont_like(100)                   # 1,013 fronts: every size bucket and the blocked path
     rng = np.random.default_rng(7)
     xs = []
-    for mode in ("1", "0"):
-        monkeypatch.setenv("QPDO_B200_CONCURRENT", mode)
+    for mode in ("1", "0", "cta"):                # "cta": big fronts solved by one CTA each instead of a cluster (same bits by design)
+        monkeypatch.setenv("QPDO_B200_CONCURRENT", "0" if mode == "0" else "1")
+        monkeypatch.setenv("QPDO_B200_SOLVE", "cta" if mode == "cta" else "cluster")
         s = qpdo_b200.QPDO()
         s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
         n, m = s.n, s.m
