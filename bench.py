@@ -186,21 +186,21 @@ def run_c3(args, dist):
     worst = dist.reduce([kkt_ms, wall / args.steps * 1e3], "max")
     pk, pk_src = peaks()
     solve_ms = prof.solve_ms / newton
-    rl = {"bound": "hbm", "kernel": "supernodal triangular solves (k_fwd/k_bwd graph)", "achieved": alg["solve_bytes"] / (solve_ms * 1e-3) / 1e9,
+    rl = {"bound": "hbm", "kernel": "supernodal triangular solves (k_fwd / k_bwd and the cluster kernels k_fwd_cl / k_bwd_cl, one graph)", "achieved": alg["solve_bytes"] / (solve_ms * 1e-3) / 1e9,
           "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s", "traffic": None}
     rl["frac"] = rl["achieved"] / rl["peak"]
     rec3 = None
     try:
         rec3 = json.load(open(os.path.join(ROOT, "profiles", "c3_ncu.json")))
         rl["traffic"] = rec3.get("solve_dram_bytes_per_newton")
-        rl["traffic_source"] = "sum of dram__bytes_read+write over the k_fwd/k_bwd launches of one Newton step, ncu: profiles/c3_ncu.json @ %s" % rec3.get("commit")
+        rl["traffic_source"] = "sum of dram__bytes_read+write over the k_fwd* / k_bwd* launches of one Newton step, ncu: profiles/c3_ncu.json @ %s" % rec3.get("commit")
     except Exception:
         pass
     # numeric factorization against the FP64 peaks measured on this device in this run (register-resident DMMA / DFMA loops)
     dm, df = C.c_double(0), C.c_double(0)
     lib.qpdo_dev_measure_fp64(dist.local, C.byref(dm), C.byref(df))
     fac_tf = alg["factor_flops"] / (prof.factor_ms / newton * 1e-3) / 1e12
-    rlf = {"bound": "tensor", "kernel": "multifrontal LDL' (k_front_smem, k_big_panel: mma.sync.m8n8k4.f64 rank-32 updates)", "achieved": fac_tf,
+    rlf = {"bound": "tensor", "kernel": "multifrontal LDL' (k_front_smem, k_big_panel: row-tile solve and rank-32 update by mma.sync.m8n8k4.f64)", "achieved": fac_tf,
            "peak": dm.value, "peak_source": "qpdo_dev_measure_fp64: mma.sync.m8n8k4.f64 loop over all SMs, this run", "dfma_peak": df.value,
            "unit": "TFLOP/s (f64)", "frac": fac_tf / dm.value if dm.value > 0 else None, "frac_of_dfma_peak": fac_tf / df.value if df.value > 0 else None,
            "flops_per_factorization": alg["factor_flops"]}
