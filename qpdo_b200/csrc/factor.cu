@@ -793,6 +793,23 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
     const double *L = (N > A.bigN ? A.Xout : A.Lx) + A.Lp[s];
     const int tid = threadIdx.x, lane = tid & 31;
     double *yb = vec + N;
+    // NT <= 256: the panel entries a thread needs for the row update of a block are staged by cp.async one block ahead
+    // (the first block behind the extend-add of the children): plain loads end up paired with their fmas by ptxas, a
+    // chain of L2 round trips per block.  RP rows per thread cover the front (N <= 64 for one warp, N <= 256 for 256).
+    constexpr bool STG = NT <= 256;
+    constexpr int RP = NT == 32 ? 2 : 1;
+    double *stage = vec + ((N + NB + 1) & ~1);
+    auto prefetch = [&](int kb_) {
+        if (STG && kb_ < nc) {
+            const int nb_ = min(NB, nc - kb_);
+#pragma unroll
+            for (int r = 0; r < RP; r++) {
+                const int i = kb_ + nb_ + tid + r * NT;
+                if (i < N) for (int k = 0; k < nb_; k++) cp_async8(stage + (k * RP + r) * NT + tid, L + (int64_t)(kb_ + k) * N + i);
+            }
+        }
+    };
+    prefetch(0);
     for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : 0.0;
     __syncthreads();
     for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
@@ -831,10 +848,13 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
         __syncthreads();
         // rows below the block: one row per thread, its NB panel entries fetched as two batches of 16
         // independent loads (the panel streams from HBM/L2 once; latency, not bandwidth, bounds one CTA)
-        for (int i = kb + nb + tid; i < N; i += NT) {
+        if (STG) cp_async_wait_all();
+        for (int i = kb + nb + tid, r = 0; i < N; i += NT, r++) {
             const double *Li = L + (int64_t)kb * N + i;
             double acc = 0.0;
-            if (nb == NB) {
+            if (STG && r < RP) {
+                for (int k = 0; k < nb; k++) acc = fma(stage[(k * RP + r) * NT + tid], yb[k], acc);
+            } else if (nb == NB) {
 #pragma unroll
                 for (int h = 0; h < NB; h += 16) {
                     double lv[16];
@@ -849,6 +869,7 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
             vec[i] -= acc;
         }
         __syncthreads();
+        prefetch(kb + NB);
     }
     double *u = A.uv + A.sn_rowptr[s];
     for (int i = tid; i < nr; i += NT) u[i] = vec[nc + i];
@@ -864,17 +885,29 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
     const double *L = (N > A.bigN ? A.Xout : A.Lx) + A.Lp[s];
     const int *rows = A.rows + A.sn_rowptr[s];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NW = NT / 32;
+    const int nblk = (nc + NB - 1) / NB;
+    // NT <= 256: the rows below a block (all its columns) are staged by cp.async one block ahead, see k_fwd
+    constexpr bool STG = NT <= 256;
+    double *stage = vec + ((N + 1) & ~1);                       // [NB][N], entry (i, kb + k) at stage[k * N + i]
+    auto prefetch = [&](int b_) {
+        if (STG && b_ >= 0) {
+            const int kb_ = b_ * NB, nb_ = min(NB, nc - kb_), R = N - kb_ - nb_;
+            for (int idx = tid; idx < nb_ * R; idx += NT) { const int k = idx / R, i = kb_ + nb_ + (idx - k * R); cp_async8(stage + k * N + i, L + (int64_t)(kb_ + k) * N + i); }
+        }
+    };
+    prefetch(nblk - 1);
     for (int i = tid; i < N; i += NT) vec[i] = (i < nc) ? A.xs[f + i] : A.xs[rows[i - nc]];
     __syncthreads();
-    const int nblk = (nc + NB - 1) / NB;
     for (int b = nblk - 1; b >= 0; b--) {
         const int kb = b * NB, nb = min(NB, nc - kb);
         for (int idx = tid; idx < nb * nb; idx += NT) { int j = idx / nb, i = idx - j * nb; D[i][j] = L[(int64_t)(kb + j) * N + kb + i]; }
+        if (STG) { cp_async_wait_all(); __syncthreads(); }      // a warp sums columns that other threads staged
         // t_k = vec[k] - sum_{i >= kb+nb} L[i,k] vec[i], one warp per column
         for (int k = wid; k < nb; k += NW) {
             const double *Lk = L + (int64_t)(kb + k) * N;
             double acc = 0.0;
             int i = kb + nb + lane;
+            if (STG) { for (; i < N; i += 32) acc = fma(stage[k * N + i], vec[i], acc); }
             for (; i + 7 * 32 < N; i += 8 * 32) {            // 8 independent loads in flight per lane
                 double lv[8];
 #pragma unroll
@@ -887,6 +920,7 @@ __global__ void __launch_bounds__(NT) k_bwd(SArgs A, const int *list)
             if (lane == 0) vec[kb + k] -= acc;
         }
         __syncthreads();
+        prefetch(b - 1);                                        // every warp is through with the stage
         if (tid < 32) {
             double v = (lane < nb) ? vec[kb + lane] : 0.0;
             if (N > A.bigN && !A.panel_v1) {
@@ -1179,6 +1213,8 @@ int factor_setup(qpdo_dev *d, int ordering)
     { const char *sv = getenv("QPDO_B200_SOLVE"); F.solve_cluster = !(sv && !strcmp(sv, "cta")); }   // "cta": one CTA per big front (A/B)
     cudaFuncSetAttribute(k_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(k_fwd<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
+    cudaFuncSetAttribute(k_bwd<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
     cudaFuncSetAttribute(k_front_smem<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_front_smem<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cudaFuncSetAttribute(k_big_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PANEL_SMEM);
@@ -1399,16 +1435,16 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
             }
             if (q > qb) {
                 cudaStream_t st = sv[br++];
-                size_t smem = sizeof(double) * (ordN(qb) + NB);
-                if (pass == 0) k_fwd<256><<<q - qb, 256, smem, st>>>(A, F.level_sn + qb);
-                else k_bwd<256><<<q - qb, 256, smem, st>>>(A, F.level_sn + qb);
+                const size_t Nm = (size_t)ordN(qb);              // + the cp.async stage: NB x 256 (forward), NB x N (backward)
+                if (pass == 0) k_fwd<256><<<q - qb, 256, sizeof(double) * (Nm + NB + 2 + NB * 256), st>>>(A, F.level_sn + qb);
+                else k_bwd<256><<<q - qb, 256, sizeof(double) * (Nm + 2 + NB * Nm), st>>>(A, F.level_sn + qb);
                 launches++;
             }
             if (e > q) {
                 cudaStream_t st = sv[br++];
-                size_t smem = sizeof(double) * (ordN(q) + NB);
-                if (pass == 0) k_fwd<32><<<e - q, 32, smem, st>>>(A, F.level_sn + q);
-                else k_bwd<32><<<e - q, 32, smem, st>>>(A, F.level_sn + q);
+                const size_t Nm = (size_t)ordN(q);
+                if (pass == 0) k_fwd<32><<<e - q, 32, sizeof(double) * (Nm + NB + 2 + NB * 64), st>>>(A, F.level_sn + q);
+                else k_bwd<32><<<e - q, 32, sizeof(double) * (Nm + 2 + NB * Nm), st>>>(A, F.level_sn + q);
                 launches++;
             }
             join_level(d, nbranch, sv);
