@@ -25,7 +25,8 @@ step "ncu c3: launch list + --set full of the frontal and solve kernels (2 loop 
 python bench.py --workload c3 --steps 1 --warmup 0 --max-iter 12 --no-cpu-baseline > $O/${TAG}_plain_c3.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file $O/${TAG}_launches_c3.csv \
     python bench.py --workload c3 --steps 1 --warmup 0 --max-iter 12 --no-cpu-baseline > $O/${TAG}_ncu_c3.log 2>&1; echo "rc=$?"
-# launches per Newton step from the launch list (24 Newton steps in that run: 2 solves x 12 passes)
+# launches per Newton step from the launch list (24 Newton steps in that run: 2 solves x 12 passes); the captures below take the
+# SECOND Newton step's launches (-s skips the first)
 NSOLVE=$(python - <<PY
 import csv
 rows=list(csv.reader(open("$O/${TAG}_launches_c3.csv")))
@@ -35,10 +36,10 @@ print(n//24)
 PY
 )
 echo "solve launches per Newton step: $NSOLVE"
-ncu --set full --clock-control none -k 'regex:k_fwd|k_bwd' -c $((2 * NSOLVE)) -f -o $O/${TAG}_c3_solve \
+ncu --set full --clock-control none -k 'regex:k_fwd|k_bwd' -s $NSOLVE -c $NSOLVE -f -o $O/${TAG}_c3_solve \
     python bench.py --workload c3 --steps 1 --warmup 0 --max-iter 3 --no-cpu-baseline > $O/${TAG}_ncu_c3solve.log 2>&1; echo "rc=$?"
 [ -f $O/${TAG}_c3_solve.ncu-rep ] && ncu -i $O/${TAG}_c3_solve.ncu-rep --page raw --csv > $O/${TAG}_c3_solve.csv 2>/dev/null && rm -f $O/${TAG}_c3_solve.ncu-rep
-ncu --set full --clock-control none -k 'regex:k_big_panel|k_big_assemble|k_front_smem' -c 230 -f -o $O/${TAG}_c3_front \
+ncu --set full --clock-control none -k 'regex:k_big_panel|k_big_assemble|k_front_smem' -s 112 -c 112 -f -o $O/${TAG}_c3_front \
     python bench.py --workload c3 --steps 1 --warmup 0 --max-iter 3 --no-cpu-baseline > $O/${TAG}_ncu_c3front.log 2>&1; echo "rc=$?"
 [ -f $O/${TAG}_c3_front.ncu-rep ] && ncu -i $O/${TAG}_c3_front.ncu-rep --page raw --csv > $O/${TAG}_c3_front.csv 2>/dev/null && rm -f $O/${TAG}_c3_front.ncu-rep
 ls -la $O | grep ${TAG}_ | tail -40
