@@ -10,6 +10,9 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <cstdlib>
+#include <atomic>
+#include <thread>
 
 namespace {
 
@@ -207,24 +210,27 @@ extern "C" int qpdo_order_mindeg(int n, const int64_t *gp, const int *gi, int *p
 // to cut (random graphs), are ordered by minimum degree on the induced subgraph.
 namespace {
 
+// State shared by all runs of the dissection.  The arrays are indexed by vertex; concurrent runs work on disjoint
+// vertex sets, BFS stamps come from one atomic counter (a vertex may carry a stale stamp of an ancestor's sweep).
 struct NDWork {
     int n;
     const int64_t *gp;
     const int *gi;
     std::vector<int> piece;      // piece id of every vertex (only vertices of the current piece carry its id)
-    std::vector<int> level;      // BFS level, valid when lstamp[v] == stamp
+    std::vector<int> level;      // BFS level, valid when lstamp[v] == the sweep's stamp
     std::vector<int> lstamp;
     std::vector<int> local;      // global -> local index inside a leaf
-    int stamp = 0;
-    std::vector<int> order;      // elimination order being built (separators are placed by the recursion)
+    std::atomic<int> stamp{0};
+    std::atomic<int> idgen{1};   // piece labels (0 = the whole graph); labels are only ever compared
+    int leaf = 256;
 };
 
 // BFS over the vertices with piece[v] == id from `root`; returns the vertices in visiting order, `ends` = level starts
 static void nd_bfs(NDWork &W, int id, int root, std::vector<int> &out, std::vector<int> &ends)
 {
     out.clear(); ends.clear();
-    W.stamp++;
-    W.lstamp[root] = W.stamp; W.level[root] = 0;
+    const int stamp = ++W.stamp;
+    W.lstamp[root] = stamp; W.level[root] = 0;
     out.push_back(root);
     size_t head = 0;
     int cur = 0;
@@ -234,18 +240,18 @@ static void nd_bfs(NDWork &W, int id, int root, std::vector<int> &out, std::vect
         if (W.level[v] != cur) { cur = W.level[v]; ends.push_back((int)head - 1); }
         for (int64_t t = W.gp[v]; t < W.gp[v + 1]; t++) {
             const int u = W.gi[t];
-            if (W.piece[u] != id || W.lstamp[u] == W.stamp) continue;
-            W.lstamp[u] = W.stamp; W.level[u] = W.level[v] + 1;
+            if (W.piece[u] != id || W.lstamp[u] == stamp) continue;
+            W.lstamp[u] = stamp; W.level[u] = W.level[v] + 1;
             out.push_back(u);
         }
     }
     ends.push_back((int)out.size());
 }
 
-static void nd_leaf(NDWork &W, const std::vector<int> &verts, int id)
+static void nd_leaf(NDWork &W, const std::vector<int> &verts, int id, std::vector<int> &order)
 {
     const int k = (int)verts.size();
-    if (k <= 2) { for (int v : verts) W.order.push_back(v); return; }
+    if (k <= 2) { for (int v : verts) order.push_back(v); return; }
     for (int i = 0; i < k; i++) W.local[verts[i]] = i;
     std::vector<int64_t> lp(k + 1, 0);
     std::vector<int> li;
@@ -255,50 +261,47 @@ static void nd_leaf(NDWork &W, const std::vector<int> &verts, int id)
         lp[i + 1] = (int64_t)li.size();
     }
     std::vector<int> lperm(k);
-    if (li.empty() || qpdo_order_mindeg(k, lp.data(), li.data(), lperm.data()) != 0) { for (int v : verts) W.order.push_back(v); return; }
-    for (int i = 0; i < k; i++) W.order.push_back(verts[lperm[i]]);
+    if (li.empty() || qpdo_order_mindeg(k, lp.data(), li.data(), lperm.data()) != 0) { for (int v : verts) order.push_back(v); return; }
+    for (int i = 0; i < k; i++) order.push_back(verts[lperm[i]]);
 }
 
-} // namespace
-
-extern "C" int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_out, int leaf)
+// Dissect the piece `V0` (its vertices carry the label `id0`) and append its elimination order to `order`.  While
+// `par` > 0 the two parts of a cut of a large piece are dissected by two threads, each with its own output, concatenated
+// in the order the one-thread run produces (first part, second part, separator): the result does not depend on `par`.
+static void nd_run(NDWork &W, std::vector<int> V0, int id0, std::vector<int> &order, int par)
 {
-    if (n <= 0) return 0;
-    if (leaf < 8) leaf = 8;
-    NDWork W;
-    W.n = n; W.gp = gp; W.gi = gi;
-    W.piece.assign(n, 0); W.level.assign(n, 0); W.lstamp.assign(n, 0); W.local.assign(n, 0);
-    W.order.reserve(n);
-    // explicit stack of tasks: {piece id, kind}; kind 0 = dissect the piece, kind 1 = emit a stored separator
-    struct Task { int id; int kind; };
+    const int64_t *gp = W.gp; const int *gi = W.gi; const int leaf = W.leaf;
+    // explicit stack of tasks: {table slot, kind}; kind 0 = dissect the piece, kind 1 = emit a stored separator
+    struct Task { int slot; int kind; };
     std::vector<Task> stack;
-    std::vector<std::vector<int>> verts(1), seps(1);        // per piece id: its vertices / its separator
-    verts[0].resize(n);
-    for (int v = 0; v < n; v++) verts[0][v] = v;
+    std::vector<std::vector<int>> verts(1), seps(1);        // per slot: the piece's vertices / its separator
+    std::vector<int> ids(1, id0);                           // per slot: the piece's label
+    verts[0].swap(V0);
     stack.push_back({0, 0});
     std::vector<int> bfs, ends, bfs2, ends2;
+    auto new_piece = [&]() { verts.emplace_back(); seps.emplace_back(); ids.push_back(W.idgen++); return (int)verts.size() - 1; };
     while (!stack.empty()) {
         const Task tk = stack.back(); stack.pop_back();
-        if (tk.kind == 1) { nd_leaf(W, seps[tk.id], -1 - tk.id); std::vector<int>().swap(seps[tk.id]); continue; }
-        const int id = tk.id;
-        std::vector<int> V; V.swap(verts[id]);
+        const int slot = tk.slot, id = ids[slot];
+        if (tk.kind == 1) { nd_leaf(W, seps[slot], -1 - id, order); std::vector<int>().swap(seps[slot]); continue; }
+        std::vector<int> V; V.swap(verts[slot]);
         const int k = (int)V.size();
         if (k == 0) continue;
-        if (k <= leaf) { nd_leaf(W, V, id); continue; }
+        if (k <= leaf) { nd_leaf(W, V, id, order); continue; }
         // connected components of the piece in one sweep (a pattern with few active rows is mostly isolated
         // vertices): small components go straight to the order, the others become pieces of their own
         nd_bfs(W, id, V[0], bfs, ends);
         if ((int)bfs.size() < k) {
-            std::vector<int> todo;                          // new piece ids, dissected in discovery order
+            std::vector<int> todo;                          // new slots, dissected in discovery order
             size_t vi = 0;
             std::vector<int> comp; comp.swap(bfs);
             for (;;) {
-                if ((int)comp.size() <= leaf && comp.size() <= 2) { for (int v : comp) { W.piece[v] = -2000000000; W.order.push_back(v); } }
+                if ((int)comp.size() <= leaf && comp.size() <= 2) { for (int v : comp) { W.piece[v] = -2000000000; order.push_back(v); } }
                 else {
-                    const int idc = (int)verts.size();
-                    verts.emplace_back(comp); seps.emplace_back();
+                    const int sc = new_piece(), idc = ids[sc];
+                    verts[sc] = comp;
                     for (int v : comp) W.piece[v] = idc;
-                    todo.push_back(idc);
+                    todo.push_back(sc);
                 }
                 while (vi < V.size() && W.piece[V[vi]] != id) vi++;
                 if (vi >= V.size()) break;
@@ -319,7 +322,7 @@ extern "C" int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_
         }
         (void)root;
         const int nlev = (int)ends.size() - 1;
-        if (nlev < 5) { nd_leaf(W, V, id); continue; }    // too shallow to cut (dense / random graph): minimum degree
+        if (nlev < 5) { nd_leaf(W, V, id, order); continue; }    // too shallow to cut (dense / random graph): minimum degree
         // separator level: among levels leaving >= 35 % on both sides the one with the fewest vertices
         int bestl = -1, bests = k + 1;
         for (int l = 1; l + 1 < nlev; l++) {
@@ -330,28 +333,59 @@ extern "C" int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_
             int bestd = k + 1;
             for (int l = 1; l + 1 < nlev; l++) { const int dlt = abs(ends[l] - (k - ends[l + 1])); if (dlt < bestd) { bestd = dlt; bestl = l; } }
         }
-        if (bestl < 0) { nd_leaf(W, V, id); continue; }
-        const int ida = (int)verts.size(), idb = ida + 1;
-        verts.emplace_back(); verts.emplace_back(); seps.emplace_back(); seps.emplace_back();
+        if (bestl < 0) { nd_leaf(W, V, id, order); continue; }
+        const int sa = new_piece(), sb = new_piece(), ida = ids[sa], idb = ids[sb];
+        std::vector<int> &Va = verts[sa], &Vb = verts[sb], &Sp = seps[slot];
         // levels carry the stamp of the BFS that is in `bfs` now: re-run it if the last probe did not win
         nd_bfs(W, id, bfs[0], bfs, ends);
         for (int t = 0; t < k; t++) {
             const int v = bfs[t], l = W.level[v];
-            if (l < bestl) { W.piece[v] = ida; verts[ida].push_back(v); }
-            else if (l > bestl) { W.piece[v] = idb; verts[idb].push_back(v); }
+            if (l < bestl) { W.piece[v] = ida; Va.push_back(v); }
+            else if (l > bestl) { W.piece[v] = idb; Vb.push_back(v); }
         }
         for (int t = ends[bestl]; t < ends[bestl + 1]; t++) {
             const int v = bfs[t];
             bool touches = false;
             for (int64_t e = gp[v]; e < gp[v + 1] && !touches; e++) touches = (W.piece[gi[e]] == idb);
-            if (touches) { W.piece[v] = -1 - id; seps[id].push_back(v); }
-            else { W.piece[v] = ida; verts[ida].push_back(v); }
+            if (touches) { W.piece[v] = -1 - id; Sp.push_back(v); }
+            else { W.piece[v] = ida; Va.push_back(v); }
         }
-        stack.push_back({id, 1});          // emitted after both parts
-        stack.push_back({idb, 0});
-        stack.push_back({ida, 0});
+        if (par > 0 && (int)Va.size() > 4096 && (int)Vb.size() > 4096) {
+            std::vector<int> oa, ob, A, B;
+            A.swap(Va); B.swap(Vb);
+            std::thread th([&W, &A, ida, &oa, par]() { nd_run(W, std::move(A), ida, oa, par - 1); });
+            nd_run(W, std::move(B), idb, ob, par - 1);
+            th.join();
+            order.insert(order.end(), oa.begin(), oa.end());
+            order.insert(order.end(), ob.begin(), ob.end());
+            nd_leaf(W, seps[slot], -1 - id, order);
+            std::vector<int>().swap(seps[slot]);
+            continue;
+        }
+        stack.push_back({slot, 1});        // emitted after both parts
+        stack.push_back({sb, 0});
+        stack.push_back({sa, 0});
     }
-    if ((int)W.order.size() != n) return -1;
-    for (int i = 0; i < n; i++) perm_out[i] = W.order[i];
+}
+
+} // namespace
+
+extern "C" int qpdo_order_nd(int n, const int64_t *gp, const int *gi, int *perm_out, int leaf)
+{
+    if (n <= 0) return 0;
+    if (leaf < 8) leaf = 8;
+    NDWork W;
+    W.n = n; W.gp = gp; W.gi = gi; W.leaf = leaf;
+    W.piece.assign(n, 0); W.level.assign(n, 0); W.lstamp.assign(n, 0); W.local.assign(n, 0);
+    std::vector<int> order; order.reserve(n);
+    std::vector<int> all(n);
+    for (int v = 0; v < n; v++) all[v] = v;
+    // QPDO_ND_THREADS: 1 = one thread; default: up to 8 (three levels of two-way forks).  Same order either way.
+    int par = 3;
+    { const char *ev = getenv("QPDO_ND_THREADS"); if (ev) { const int t = atoi(ev); par = t <= 1 ? 0 : (t < 4 ? 1 : (t < 8 ? 2 : 3)); } }
+    if (std::thread::hardware_concurrency() < 2) par = 0;
+    nd_run(W, std::move(all), 0, order, par);
+    if ((int)order.size() != n) return -1;
+    for (int i = 0; i < n; i++) perm_out[i] = order[i];
     return 0;
 }

@@ -1,5 +1,7 @@
 // symbolic.cpp -- see symbolic.h.  Host-side, runs once per qpdo_setup.
 #include "symbolic.h"
+#include <thread>
+#include <atomic>
 #include <vector>
 #include <algorithm>
 #include <numeric>
@@ -322,15 +324,38 @@ extern "C" qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, con
         }
     // products a_ir * a_ic grouped by K entry, constraint rows in ascending order inside a group
     std::vector<int64_t> Ktp(nnzK + 1, 0);
-    std::vector<int> pair_e; pair_e.reserve((size_t)pairs);
-    for (int r = 0; r < m; r++)
-        for (int64_t t1 = Rp[r]; t1 < Rp[r + 1]; t1++)
-            for (int64_t t2 = t1; t2 < Rp[r + 1]; t2++) {
-                int a = pinv[Rj[t1]], b = pinv[Rj[t2]];
-                int e = find_entry(std::max(a, b), std::min(a, b));
-                if (e < 0) { if (err) snprintf(err, 256, "symbolic: A'A entry missing from K pattern"); return NULL; }
-                pair_e.push_back(e); Ktp[e + 1]++;
+    // pass 1 (the binary searches): rows split over threads, every row writes its own stretch of pair_e
+    std::vector<int64_t> prow((size_t)m + 1, 0);
+    for (int r = 0; r < m; r++) { const int64_t d = Rp[r + 1] - Rp[r]; prow[r + 1] = prow[r] + d * (d + 1) / 2; }
+    std::vector<int> pair_e((size_t)prow[m]);
+    {
+        int nth = (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency()));
+        if (prow[m] < 100000) nth = 1;
+        { const char *ev = getenv("QPDO_SYM_THREADS"); if (ev && atoi(ev) >= 1) nth = std::min(nth, atoi(ev)); }
+        std::atomic<int> missing(0);
+        auto work = [&](int r0, int r1) {
+            for (int r = r0; r < r1; r++) {
+                int64_t g = prow[r];
+                for (int64_t t1 = Rp[r]; t1 < Rp[r + 1]; t1++)
+                    for (int64_t t2 = t1; t2 < Rp[r + 1]; t2++) {
+                        int a = pinv[Rj[t1]], b = pinv[Rj[t2]];
+                        int e = find_entry(std::max(a, b), std::min(a, b));
+                        if (e < 0) { missing = 1; e = 0; }
+                        pair_e[g++] = e;
+                        __atomic_fetch_add(&Ktp[e + 1], (int64_t)1, __ATOMIC_RELAXED);
+                    }
             }
+        };
+        std::vector<std::thread> th;
+        for (int t = 1; t < nth; t++) {                     // equal shares of the pairs, not of the rows
+            const int r0 = (int)(std::lower_bound(prow.begin(), prow.end(), prow[m] * t / nth) - prow.begin());
+            const int r1 = (int)(std::lower_bound(prow.begin(), prow.end(), prow[m] * (t + 1) / nth) - prow.begin());
+            th.emplace_back(work, std::min(r0, m), t + 1 == nth ? m : std::min(r1, m));
+        }
+        work(0, nth > 1 ? std::min((int)(std::lower_bound(prow.begin(), prow.end(), prow[m] / nth) - prow.begin()), m) : m);
+        for (auto &x : th) x.join();
+        if (missing) { if (err) snprintf(err, 256, "symbolic: A'A entry missing from K pattern"); return NULL; }
+    }
     for (int64_t e = 0; e < nnzK; e++) Ktp[e + 1] += Ktp[e];
     const int64_t ntriple = Ktp[nnzK];
     std::vector<int> Kt_row(ntriple ? ntriple : 1), Kt_a1(ntriple ? ntriple : 1), Kt_a2(ntriple ? ntriple : 1);

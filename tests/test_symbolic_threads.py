@@ -1,0 +1,48 @@
+"""Host symbolic analysis (csrc/ordering.cpp, csrc/symbolic.cpp): the nested dissection forks its two parts onto threads and
+the K-product map splits its searches over threads -- the result must not depend on the thread count (the numerics of every
+golden depend on the ordering).  CPU only."""
+import ctypes as C
+import hashlib
+import os
+import sys
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+from qpdo_b200 import problems
+
+
+def _digest(lib, p, ordering=2):
+    import order_stats as o
+    P = C.POINTER
+    lib.qpdo_symbolic_analyze.restype = P(o.Sym)
+    lib.qpdo_symbolic_analyze.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_char_p]
+    lib.qpdo_symbolic_free.argtypes = [P(o.Sym)]
+    Q = sp.tril(sp.csc_matrix(p["Q"]), format="csc"); Q.sort_indices()
+    A = sp.csc_matrix(p["A"]); A.sort_indices()
+    n, m = Q.shape[0], A.shape[0]
+    a = [np.ascontiguousarray(v, dtype=np.int32) for v in (Q.indptr, Q.indices, A.indptr, A.indices)]
+    err = C.create_string_buffer(256)
+    Sp = lib.qpdo_symbolic_analyze(n, m, *[v.ctypes.data for v in a], ordering, err)
+    assert Sp, err.value
+    S = Sp.contents
+    h = hashlib.sha1()
+    for name, cnt in (("perm", n), ("Kdst", S.nnzK), ("Ktp", S.nnzK + 1), ("Kt_row", S.ntriple), ("Kt_a1", S.ntriple), ("Kt_a2", S.ntriple),
+                      ("rel", S.sn_rowptr[S.nsuper]), ("level_sn", S.nsuper), ("sn_start", S.nsuper + 1)):
+        if cnt:
+            h.update(np.ctypeslib.as_array(getattr(S, name), shape=(cnt,)).tobytes())
+    lib.qpdo_symbolic_free(Sp)
+    return h.hexdigest()
+
+
+@pytest.mark.parametrize("gen", ["cont120", "lasso", "rand"])
+def test_symbolic_structure_does_not_depend_on_the_thread_count(cuda_lib, gen, monkeypatch):
+    p = {"cont120": lambda: problems.cont_like(120), "lasso": lambda: problems.lasso_dual(n=20000, m=10000),
+         "rand": lambda: problems.random_qp(1000, 500, 0.01, seed=1)}[gen]()
+    out = []
+    for nd, sym in (("1", "1"), ("8", "8"), ("4", "2"), ("8", "8")):
+        monkeypatch.setenv("QPDO_ND_THREADS", nd)
+        monkeypatch.setenv("QPDO_SYM_THREADS", sym)
+        out.append(_digest(cuda_lib, p))
+    assert len(set(out)) == 1, out
