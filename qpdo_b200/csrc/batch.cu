@@ -10,9 +10,10 @@
 // on the host (symbolic.cpp) and every CTA follows the same elimination program.
 //
 // Layout: per-instance inputs are instance-major in HBM (coalesced per CTA); per-CTA state is
-// ~(nnzA + nnzQ + 12 n + 16 m + n(n+1)/2) doubles of shared memory (80 KB for n=100, m=150: two CTAs
-// per SM).  K is a packed dense lower triangle in the permuted order; the linesearch scratch
-// aliases it (K is dead once dx is known).  CTAs are persistent and pull instances from an atomic
+// ~(nnzA + nnzQ + 12 n + 16 m + |L|) doubles of shared memory (53 KB for n=100, m=150: four CTAs per SM,
+// which registers allow as well).  L is kept as packed trapezoids of the supernodes in the permuted order; the
+// linesearch scratch lives in vectors that are dead during the linesearch (L survives the step, so an unchanged K is
+// not factored again).  CTAs are persistent and pull instances from an atomic
 // work queue (iteration counts are ragged).  Compiled with -fmad=false: element-wise arithmetic
 // rounds like the reference's scalar C; fma() is used only inside the factorization / solves.
 #include "dev_internal.h"

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
     // (row values u_i^t stay in registers across the columns), a_ij = fma(-u^3, l^3, fma(... fma(-u^0, l^0, a_ij)))
     // -- the same ascending-k fma sequence per entry as a column-by-column elimination, with a quarter of
     // the shared-memory traffic and barriers.
-    constexpr int KB = 4, RMAX = 5;                        // fronts up to 32 * RMAX = 160 rows
+    constexpr int KB = 4, RMAX = NT == 64 ? 1 : (NT == 128 ? 2 : 5);   // row chunks of 32: N <= 32 / 64 / 150 by size class (fewer registers, more resident CTAs for the small ones)
     const int lane = tid & 31, wid = tid >> 5, NW = NT / 32;
     double *ub = F + (size_t)ld * N, *lb = ub + KB * N;
     for (int kb = 0; kb < nc; kb += KB) {
@@ -148,8 +148,9 @@ __global__ void __launch_bounds__(NT) k_front_smem(FArgs A, const int *list)
             bool bad = false;
 #pragma unroll
             for (int t = 0; t < KB; t++) {
+                if (t >= nk) { u[t] = 0.0; l[t] = 0.0; continue; }     // (CTA-uniform: fronts with one or two pivots pay for one or two)
                 const double dt = P[t][t];
-                bad = bad || (t < nk && !(dt > 0.0));
+                bad = bad || !(dt > 0.0);
                 const double rt = __drcp_rn(dt);
                 double L[KB];
 #pragma unroll
@@ -779,6 +780,7 @@ struct SArgs {
     const int64_t *sn_rowptr, *Lp;
     const double *Lx, *Xout;   // fronts of order N > bigN read their panel from Xout
     int bigN, panel_v1;        // panel_v1: no inverse diagonal blocks in Xout (round-1 panel step)
+    int stage_rows;            // k_fwd<32 | 256>: row stride of the cp.async stage (set per launch)
     double *xs, *uv;
 };
 // forward: (assembled) t = b_s + children's updates; y_s = L11^{-1} t (unit lower); z_s = D^{-1} y_s is stored;
@@ -798,14 +800,15 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
     // chain of L2 round trips per block.  RP rows per thread cover the front (N <= 64 for one warp, N <= 256 for 256).
     constexpr bool STG = NT <= 256;
     constexpr int RP = NT == 32 ? 2 : 1;
-    double *stage = vec + ((N + NB + 1) & ~1);
+    const int SR = A.stage_rows;                        // rows of the stage = order of the largest front of the launch (<= RP * NT)
+    double *stage = vec + ((N + NB + 1) & ~1);         // [NB][SR], row i of block kb_ at column i - kb_ - nb_
     auto prefetch = [&](int kb_) {
         if (STG && kb_ < nc) {
             const int nb_ = min(NB, nc - kb_);
 #pragma unroll
             for (int r = 0; r < RP; r++) {
-                const int i = kb_ + nb_ + tid + r * NT;
-                if (i < N) for (int k = 0; k < nb_; k++) cp_async8(stage + (k * RP + r) * NT + tid, L + (int64_t)(kb_ + k) * N + i);
+                const int o = tid + r * NT, i = kb_ + nb_ + o;
+                if (i < N) for (int k = 0; k < nb_; k++) cp_async8(stage + k * SR + o, L + (int64_t)(kb_ + k) * N + i);
             }
         }
     };
@@ -853,7 +856,7 @@ __global__ void __launch_bounds__(NT) k_fwd(SArgs A, const int *list)
             const double *Li = L + (int64_t)kb * N + i;
             double acc = 0.0;
             if (STG && r < RP) {
-                for (int k = 0; k < nb; k++) acc = fma(stage[(k * RP + r) * NT + tid], yb[k], acc);
+                for (int k = 0; k < nb; k++) acc = fma(stage[k * SR + tid + r * NT], yb[k], acc);
             } else if (nb == NB) {
 #pragma unroll
                 for (int h = 0; h < NB; h += 16) {
@@ -1144,7 +1147,7 @@ static SArgs sargs(qpdo_dev *d)
     Factor &F = d->F;
     SArgs A;
     A.sn_start = F.sn_start; A.sn_nr = F.sn_nr; A.rel = F.rel; A.rows = F.rows; A.child_ptr = F.child_ptr;
-    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.Xout = F.Xout; A.bigN = BUCKET_N[3]; A.panel_v1 = F.panel_v1 ? 1 : 0; A.xs = F.xs; A.uv = F.uv;
+    A.child_idx = F.child_idx; A.sn_rowptr = F.sn_rowptr; A.Lp = F.Lp; A.Lx = F.Lx; A.Xout = F.Xout; A.bigN = BUCKET_N[3]; A.panel_v1 = F.panel_v1 ? 1 : 0; A.stage_rows = 0; A.xs = F.xs; A.uv = F.uv;
     return A;
 }
 
@@ -1435,15 +1438,17 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
             }
             if (q > qb) {
                 cudaStream_t st = sv[br++];
-                const size_t Nm = (size_t)ordN(qb);              // + the cp.async stage: NB x 256 (forward), NB x N (backward)
-                if (pass == 0) k_fwd<256><<<q - qb, 256, sizeof(double) * (Nm + NB + 2 + NB * 256), st>>>(A, F.level_sn + qb);
+                const size_t Nm = (size_t)ordN(qb);              // + the cp.async stage: NB x rows of the largest front
+                SArgs As = A; As.stage_rows = (int)((Nm + 1) & ~(size_t)1);
+                if (pass == 0) k_fwd<256><<<q - qb, 256, sizeof(double) * (Nm + NB + 2 + NB * (size_t)As.stage_rows), st>>>(As, F.level_sn + qb);
                 else k_bwd<256><<<q - qb, 256, sizeof(double) * (Nm + 2 + NB * Nm), st>>>(A, F.level_sn + qb);
                 launches++;
             }
             if (e > q) {
                 cudaStream_t st = sv[br++];
                 const size_t Nm = (size_t)ordN(q);
-                if (pass == 0) k_fwd<32><<<e - q, 32, sizeof(double) * (Nm + NB + 2 + NB * 64), st>>>(A, F.level_sn + q);
+                SArgs As = A; As.stage_rows = (int)((Nm + 1) & ~(size_t)1);
+                if (pass == 0) k_fwd<32><<<e - q, 32, sizeof(double) * (Nm + NB + 2 + NB * (size_t)As.stage_rows), st>>>(As, F.level_sn + q);
                 else k_bwd<32><<<e - q, 32, sizeof(double) * (Nm + 2 + NB * Nm), st>>>(A, F.level_sn + q);
                 launches++;
             }

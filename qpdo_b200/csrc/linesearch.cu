@@ -238,7 +238,7 @@ __global__ void k_ls_reduce(const double *part, int nblk, qpdo_dev_scalars *sc, 
 // LSD radix sort, 8-bit digits, stable.  Tile = 2048 keys per CTA, 8 warps x 8 rows of 32.
 // Per-warp digit counts come from __match_any_sync; the scatter pass recomputes them so that the
 // rank of every key inside its tile follows the original order.
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const unsigned long long *key, int N, int shift, unsigned *hist, int nblk)
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const unsigned long long *key, int N, int shift, unsigned *hist, int nblk, unsigned *tot)
 {
     __shared__ unsigned cnt[256];
     const int tid = threadIdx.x;
@@ -249,49 +249,38 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const unsigned long 
         atomicAdd(&cnt[(unsigned)(key[k] >> shift) & 255u], 1u);
     __syncthreads();
     hist[(size_t)tid * nblk + blockIdx.x] = cnt[tid];
+    if (cnt[tid]) atomicAdd(&tot[tid], cnt[tid]);              // digit totals of the pass (integers: order does not matter)
 }
-__global__ void __launch_bounds__(1024) k_sort_scan(unsigned *hist, int total)
-{   // exclusive scan, in place, single CTA
-    __shared__ unsigned ws[32];
-    const int tid = threadIdx.x, per = (total + 1023) / 1024;
-    const int b = tid * per, e = min(total, b + per);
-    unsigned s = 0;
-    for (int i = b; i < e; i++) s += hist[i];
-    unsigned p = s;
-    const int lane = tid & 31, wid = tid >> 5;
-    for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, p, o); if (lane >= o) p += t; }
-    if (lane == 31) ws[wid] = p;
-    __syncthreads();
-    unsigned off = 0;
-    for (int w = 0; w < wid; w++) off += ws[w];
-    unsigned run = off + p - s;
-    for (int i = b; i < e; i++) { unsigned v = hist[i]; hist[i] = run; run += v; }
-}
-// same scan with the table staged in shared memory (coalesced in, thread-sequential over an odd-stride chunk,
-// coalesced out): the global version is a chain of dependent L2 round trips, 40 us at 2m = 360,600
-#define SCAN_SMEM_MAX_PER 55     // 1024 chunks of at most this many entries fit 227 KB
-__global__ void __launch_bounds__(1024) k_sort_scan_smem(unsigned *hist, int total, int per)
+// Exclusive scan of the digit-major table hist[digit][block], in place: one CTA per digit.  The start of a digit's row is
+// the sum of the totals of the smaller digits (256 values, accumulated by k_sort_hist), the row itself is scanned in
+// chunks of 256 with a carry.  (Round 1 scanned the whole table in ONE CTA: 17 us per pass at 2m = 360,600, the
+// largest single item of the linesearch.)
+__global__ void __launch_bounds__(256) k_sort_scan_rows(unsigned *hist, const unsigned *tot, int nblk)
 {
-    extern __shared__ unsigned sh[];
-    __shared__ unsigned ws[32];
-    const int tid = threadIdx.x, perp = per | 1;
-    for (int i = tid; i < total; i += 1024) sh[(i / per) * perp + (i % per)] = hist[i];
+    __shared__ unsigned ws[8];
+    __shared__ unsigned carry_s;
+    const int d = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    unsigned v = (tid < d) ? tot[tid] : 0u;
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) ws[wid] = v;
     __syncthreads();
-    const int b = tid * per, cnt = max(0, min(total - b, per));
-    unsigned *mine = sh + tid * perp;
-    unsigned s = 0;
-    for (int j = 0; j < cnt; j++) s += mine[j];
-    unsigned p = s;
-    const int lane = tid & 31, wid = tid >> 5;
-    for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, p, o); if (lane >= o) p += t; }
-    if (lane == 31) ws[wid] = p;
+    if (tid == 0) { unsigned b = 0; for (int w = 0; w < 8; w++) b += ws[w]; carry_s = b; }
     __syncthreads();
-    unsigned off = 0;
-    for (int w = 0; w < wid; w++) off += ws[w];
-    unsigned run = off + p - s;
-    for (int j = 0; j < cnt; j++) { const unsigned v = mine[j]; mine[j] = run; run += v; }
-    __syncthreads();
-    for (int i = tid; i < total; i += 1024) hist[i] = sh[(i / per) * perp + (i % per)];
+    unsigned *row = hist + (size_t)d * nblk;
+    for (int c0 = 0; c0 < nblk; c0 += 256) {
+        const int i = c0 + tid;
+        const unsigned x = (i < nblk) ? row[i] : 0u;
+        unsigned p = x;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, p, o); if (lane >= o) p += t; }
+        __syncthreads();                                         // ws / carry_s of the previous chunk consumed
+        if (lane == 31) ws[wid] = p;
+        __syncthreads();
+        unsigned off = carry_s;
+        for (int w = 0; w < wid; w++) off += ws[w];
+        if (i < nblk) row[i] = off + p - x;
+        __syncthreads();
+        if (tid == 255) carry_s = off + p;
+    }
 }
 __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const unsigned long long *key, const int *idx, int N, int shift,
                                                               const unsigned *hist, int nblk, unsigned long long *okey, int *oidx)
@@ -404,8 +393,6 @@ __global__ void k_sweep_final(const double *cand, int nblk, const double *bs, co
 // =============================================================================== host side
 int linesearch_setup(qpdo_dev *d)
 {
-    // function attributes are per device: set for the device of every new context (no process-wide flag)
-    CUDA_OK(cudaFuncSetAttribute(k_sort_scan_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(unsigned) * 1024 * (SCAN_SMEM_MAX_PER | 1))));
     const size_t M2 = 2 * (size_t)d->m;
     d->sort_blocks = std::max(1, cdiv((long)M2, SORT_TILE));
     d->ls_blocks = std::max(1, std::min(592, cdiv(std::max(d->n, 2 * d->m), 256)));
@@ -413,7 +400,7 @@ int linesearch_setup(qpdo_dev *d)
         dev_alloc(d, &d->ls_key[1], M2) || dev_alloc(d, &d->ls_idx[0], M2) || dev_alloc(d, &d->ls_idx[1], M2) ||
         dev_alloc(d, &d->ls_part, (size_t)d->ls_blocks * LS_PART + 8) ||
         dev_alloc(d, &d->ls_scan, (size_t)d->sort_blocks * 5 + 8) ||
-        dev_alloc(d, &d->ls_hist, (size_t)d->sort_blocks * 256))
+        dev_alloc(d, &d->ls_hist, (size_t)d->sort_blocks * 256 + 8 * 256))
         return -1;
     return 0;
 }
@@ -436,12 +423,12 @@ int linesearch_run(qpdo_dev *d)
     k_ls_build<<<d->ls_blocks, 256, 0, d->st>>>(A, d->ls_part);
     k_ls_reduce<<<1, 256, 0, d->st>>>(d->ls_part, d->ls_blocks, d->sc, ab);
     int cur = 0;
+    unsigned *tot = d->ls_hist + (size_t)nsb * 256;            // [8][256] digit totals, one row per pass
+    CUDA_OK(cudaMemsetAsync(tot, 0, sizeof(unsigned) * 8 * 256, d->st));
     for (int pass = 0; pass < 8; pass++) {
         const int shift = 8 * pass;
-        k_sort_hist<<<nsb, SORT_THREADS, 0, d->st>>>(d->ls_key[cur], M2, shift, d->ls_hist, nsb);
-        const int total = 256 * nsb, per = (total + 1023) / 1024;
-        if (per <= SCAN_SMEM_MAX_PER) k_sort_scan_smem<<<1, 1024, sizeof(unsigned) * 1024 * (size_t)(per | 1), d->st>>>(d->ls_hist, total, per);
-        else k_sort_scan<<<1, 1024, 0, d->st>>>(d->ls_hist, total);
+        k_sort_hist<<<nsb, SORT_THREADS, 0, d->st>>>(d->ls_key[cur], M2, shift, d->ls_hist, nsb, tot + 256 * pass);
+        k_sort_scan_rows<<<256, 256, 0, d->st>>>(d->ls_hist, tot + 256 * pass, nsb);
         k_sort_scatter<<<nsb, SORT_THREADS, 0, d->st>>>(d->ls_key[cur], d->ls_idx[cur], M2, shift, d->ls_hist, nsb,
                                                         d->ls_key[cur ^ 1], d->ls_idx[cur ^ 1]);
         cur ^= 1;
@@ -451,6 +438,6 @@ int linesearch_run(qpdo_dev *d)
     k_sweep_scan<<<1, 32, 0, d->st>>>(bs, nsb);
     k_sweep_find<<<nsb, 256, 0, d->st>>>(d->ls_key[cur], d->ls_idx[cur], d->ls_delta, d->ls_alpha, d->sc, bs, ab, cand);
     k_sweep_final<<<1, 32, 0, d->st>>>(cand, nsb, bs, ab, d->sc);
-    d->prof.kernel_launches += 2 + 24 + 4;
+    d->prof.kernel_launches += 2 + 1 + 24 + 4;
     return 0;
 }
