@@ -57,6 +57,7 @@ struct Factor {
     // independent launches of one tree level (size buckets, blocked fronts) run on forked streams inside the captured graphs
     cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool pdl = true;                              // panel steps chained by programmatic dependent launch (QPDO_B200_PDL=0: off)
     bool solve_cluster = true;                    // big fronts solved by a cluster of CTAs (QPDO_B200_SOLVE=cta: one CTA each)
     bool concurrent = true;                       // QPDO_B200_CONCURRENT=0: one stream (A/B measurements)
     bool panel_v1 = false;                        // QPDO_B200_PANEL=v1: round-1 panel step (A/B measurements)

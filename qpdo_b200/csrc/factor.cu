@@ -247,6 +247,10 @@ __device__ __forceinline__ double *front_elem(const FArgs &A, int s, int nc, int
 // (Measured: 23 us per level whatever the inner structure -- a variant with the destination columns in shared memory and
 // the children's row maps staged by cp.async ran at the same speed.  ncu: 50 % long-scoreboard stalls, 12-14 MB from DRAM
 // per launch: a chain of dependent loads of cold data (front descriptor -> child list -> row maps -> columns).)
+// HOIST (launches with a handful of fronts: the top of the tree, where this kernel sits on the serial chain): the symbolic
+// prologue runs before griddepcontrol.wait.  Launches with many fronts keep the searches inside the child loop: the extra
+// registers of the hoisted form cost occupancy there (C3: 40 us per factorization).
+template <bool HOIST>
 __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
 {
     const int s = list[blockIdx.x];
@@ -254,17 +258,50 @@ __global__ void __launch_bounds__(256) k_big_assemble(FArgs A, const int *list)
     const int c0 = blockIdx.y * CW;
     if (c0 >= N) return;
     const int c1 = min(N, c0 + CW), tid = threadIdx.x;
+    // Everything that depends only on the symbolic structure -- child list, row maps, the first source column of every child
+    // that falls into [c0, c1) (a lower-bound search: ~10 dependent loads) -- is done BEFORE griddepcontrol.wait, i.e. while
+    // the last panel step of the level below is still running when this launch carries the programmatic-launch attribute.
+    constexpr int MAXC = HOIST ? 8 : 1;
+    const int t0 = A.child_ptr[s], nch = A.child_ptr[s + 1] - t0;
+    int lo_c[MAXC], hi_c[MAXC];
+    const int *rl_c[MAXC];
+    if (HOIST) {
+#pragma unroll
+        for (int q = 0; q < MAXC; q++) {
+            lo_c[q] = 0; hi_c[q] = 0; rl_c[q] = A.rel;
+            if (q < nch) { const int c = A.child_idx[t0 + q]; hi_c[q] = A.sn_nr[c]; rl_c[q] = A.rel + A.sn_rowptr[c]; }
+        }
+        for (bool more = true; more;) {                // the searches of all children in lockstep: one round trip per probe level
+            more = false;
+#pragma unroll
+            for (int q = 0; q < MAXC; q++)
+                if (lo_c[q] < hi_c[q]) {
+                    const int mid = (lo_c[q] + hi_c[q]) >> 1;
+                    if (rl_c[q][mid] < c0) lo_c[q] = mid + 1; else hi_c[q] = mid;
+                    more = true;
+                }
+        }
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     for (int j = max(c0, nc); j < c1; j++) {
         double *col = A.Ux + A.Up[s] + (int64_t)(j - nc) * nr;
         for (int i = j - nc + tid; i < nr; i += 256) col[i] = 0.0;
     }
     __syncthreads();
-    for (int t = A.child_ptr[s]; t < A.child_ptr[s + 1]; t++) {
-        const int c = A.child_idx[t], rc = A.sn_nr[c];
+#pragma unroll 1
+    for (int q = 0; q < nch; q++) {
+        const int c = A.child_idx[t0 + q], rc = A.sn_nr[c];
         const int *rl = A.rel + A.sn_rowptr[c];
         const double *U = A.Ux + A.Up[c];
-        int lo = 0, hi = rc;                       // first jj with rl[jj] >= c0
-        while (lo < hi) { int mid = (lo + hi) >> 1; if (rl[mid] < c0) lo = mid + 1; else hi = mid; }
+        int lo;
+        if (HOIST && q < MAXC) {
+            lo = lo_c[0];
+#pragma unroll
+            for (int z = 1; z < MAXC; z++) if (q == z) lo = lo_c[z];
+        } else {
+            int hi = rc; lo = 0;
+            while (lo < hi) { int mid = (lo + hi) >> 1; if (rl[mid] < c0) lo = mid + 1; else hi = mid; }
+        }
         // one warp per source column, 8 independent read-modify-writes in flight per lane (the extend-add
         // is a chain of dependent global accesses: index -> address -> load -> store)
         for (int jj = lo + (tid >> 5); jj < rc; jj += 8) {
@@ -520,6 +557,11 @@ __global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int
     if (probe_on && threadIdx.x == 0) { pr[14] = gtimer(); }
     PROBE(0);
 #endif
+    // Programmatic dependent launch: the next panel step of the chain may be launched as soon as every CTA of this one has
+    // got here (its CTAs become resident on idle SMs only: this kernel is register-limited to one CTA per SM) and does its
+    // own prologue -- descriptors, tile indices -- while this step computes; it waits below, before its first read of
+    // data this step writes.  Without the launch attribute both instructions do nothing.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     FrontDesc fd;
     if (PF.count) fd = PF.d[blockIdx.x]; else fd = A.fdesc[list[blockIdx.x]];
     const int nc = fd.nc, nr = fd.nr, N = nc + nr;
@@ -542,6 +584,7 @@ __global__ void __launch_bounds__(256) k_big_panel(FArgs A, const int *list, int
     const int ra = r0 + ti * TS, rb = r0 + tj * TS;
     const bool diag_tile = (ti == tj);
     if (tid == 0) PROBE(1);
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // the previous step of the chain (or the extend-add) is complete and visible
     // ---- warp 0: the diagonal block first (lane = row, a[j] = entry (lane, j)); the loads fly while the addresses of
     // the destination tile are worked out, the identity padding beyond nb is applied when they are first used
     double a[NB];
@@ -1213,6 +1256,7 @@ int factor_setup(qpdo_dev *d, int ordering)
     }
     if (cudaEventCreateWithFlags(&F.ev_fork, cudaEventDisableTiming) != cudaSuccess) { qpdo_set_error("factor_setup: event creation failed"); return -1; }
     { const char *cv = getenv("QPDO_B200_CONCURRENT"); F.concurrent = !(cv && !strcmp(cv, "0")); }
+    { const char *pv = getenv("QPDO_B200_PDL"); F.pdl = !(pv && !strcmp(pv, "0")); }                           // 0: plain stream order between panel steps (A/B)
     { const char *sv = getenv("QPDO_B200_SOLVE"); F.solve_cluster = !(sv && !strcmp(sv, "cta")); }   // "cta": one CTA per big front (A/B)
     cudaFuncSetAttribute(k_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
@@ -1376,7 +1420,15 @@ static long issue_factor(qpdo_dev *d)
             const int *list = F.level_sn + L.first;
             cudaStream_t st = sv[br++];
             if (L.kind == 2) {
-                k_big_assemble<<<dim3(L.count, cdiv(L.maxN, CW)), 256, 0, st>>>(A, list); launches++;
+                {
+                    cudaLaunchConfig_t cfg = {};
+                    cfg.gridDim = dim3(L.count, cdiv(L.maxN, CW)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+                    cudaLaunchAttribute at[1];
+                    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+                    cfg.attrs = at; cfg.numAttrs = F.pdl ? 1 : 0;
+                    if (L.count <= 4) cudaLaunchKernelEx(&cfg, k_big_assemble<true>, A, list); else cudaLaunchKernelEx(&cfg, k_big_assemble<false>, A, list);
+                    launches++;
+                }
                 for (int kb = 0; kb < L.maxnc; kb += NB) {
                     const int R = L.maxN - kb - 1, nt = R > 0 ? cdiv(R, TS) : 0;
                     if (F.panel_v1) k_big_panel_v1<<<dim3(L.count, std::max(1, nt * (nt + 1) / 2)), 256, 0, st>>>(A, list, kb);
@@ -1389,7 +1441,12 @@ static long issue_factor(qpdo_dev *d)
                                 PF.d[t].Lp = S->Lp[sn]; PF.d[t].Up = S->Up[sn]; PF.d[t].nc = S->sn_start[sn + 1] - S->sn_start[sn]; PF.d[t].nr = S->sn_nr[sn];
                             }
                         }
-                        k_big_panel<<<dim3(L.count, 1 + nt * (nt + 1) / 2), 256, PANEL_SMEM, st>>>(A, list, kb, PF);
+                        cudaLaunchConfig_t cfg = {};
+                        cfg.gridDim = dim3(L.count, 1 + nt * (nt + 1) / 2); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = PANEL_SMEM; cfg.stream = st;
+                        cudaLaunchAttribute at[1];
+                        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+                        cfg.attrs = at; cfg.numAttrs = F.pdl ? 1 : 0;
+                        cudaLaunchKernelEx(&cfg, k_big_panel, A, list, kb, PF);
                     }
                     launches++;
                 }
