@@ -57,6 +57,8 @@ struct Factor {
     // independent launches of one tree level (size buckets, blocked fronts) run on forked streams inside the captured graphs
     cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+    int nsing = 0;                                // singleton leaf fronts at the tail of level 0 (element-wise kernels)
+    bool no_singletons = false;                   // QPDO_B200_SINGLETONS=0
     bool pdl = true;                              // panel steps chained by programmatic dependent launch (QPDO_B200_PDL=0: off)
     bool solve_cluster = true;                    // big fronts solved by a cluster of CTAs (QPDO_B200_SOLVE=cta: one CTA each)
     bool concurrent = true;                       // QPDO_B200_CONCURRENT=0: one stream (A/B measurements)

@@ -1160,6 +1160,21 @@ __global__ void __cluster_dims__(SC, 1, 1) __launch_bounds__(ST) k_bwd_cl(SArgs 
     cl.sync();
 }
 
+// ---- singleton leaf fronts -----------------------------------------------------------------------------------------
+// A column of K with no off-diagonal entry (Lasso-type problems outside the active rows: nearly all of n) is a front of
+// one pivot with no rows below and no children: its factorization is the sign check of the pivot, its forward solve one
+// division, its backward solve nothing.  They form the tail of level 0 (fronts are sorted by decreasing order) and are
+// handled element-wise, one thread per front, instead of one CTA each (same operations: xs = xs / d as in k_fwd).
+__global__ void k_single_check(FArgs A, const int *list, int count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count && !(A.Lx[A.fdesc[list[i]].Lp] > 0.0)) A.sc->not_posdef = 1;
+}
+__global__ void k_single_fwd(SArgs A, const int *list, int count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) { const int s = list[i], f = A.sn_start[s]; A.xs[f] = A.xs[f] / A.Lx[A.Lp[s]]; }
+}
 __global__ void k_permute_in(const double *rhs, const int *perm, double *xs, int n)
 {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1257,6 +1272,7 @@ int factor_setup(qpdo_dev *d, int ordering)
     if (cudaEventCreateWithFlags(&F.ev_fork, cudaEventDisableTiming) != cudaSuccess) { qpdo_set_error("factor_setup: event creation failed"); return -1; }
     { const char *cv = getenv("QPDO_B200_CONCURRENT"); F.concurrent = !(cv && !strcmp(cv, "0")); }
     { const char *pv = getenv("QPDO_B200_PDL"); F.pdl = !(pv && !strcmp(pv, "0")); }                           // 0: plain stream order between panel steps (A/B)
+    { const char *nv = getenv("QPDO_B200_SINGLETONS"); F.no_singletons = nv && !strcmp(nv, "0"); }             // 0: singleton fronts through the per-front kernels (A/B)
     { const char *sv = getenv("QPDO_B200_SOLVE"); F.solve_cluster = !(sv && !strcmp(sv, "cta")); }   // "cta": one CTA per big front (A/B)
     cudaFuncSetAttribute(k_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
@@ -1333,9 +1349,15 @@ static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
     }
     // launch plan: per level, fronts are sorted by decreasing order N
     F.plan.assign(S->nlevel, std::vector<FrontLaunch>());
+    F.nsing = 0;
     for (int lv = 0; lv < S->nlevel; lv++) {
         int b = S->level_ptr[lv], e = S->level_ptr[lv + 1];
         auto ordN = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s] + S->sn_nr[s]; };
+        if (lv == 0 && !F.no_singletons) {                     // singleton leaf fronts: the tail of level 0, element-wise kernels
+            while (e > b && ordN(e - 1) == 1) e--;
+            F.nsing = S->level_ptr[1] - e;
+            if (F.nsing) { FrontLaunch L; L.first = e; L.count = F.nsing; L.kind = 3; L.maxN = 1; L.maxnc = 1; F.plan[lv].push_back(L); }
+        }
         auto ncOf = [&](int pos) { int s = S->level_sn[pos]; return S->sn_start[s + 1] - S->sn_start[s]; };
         int pos = b;
         // big fronts first
@@ -1419,7 +1441,8 @@ static long issue_factor(qpdo_dev *d)
         for (const FrontLaunch &L : F.plan[lv]) {
             const int *list = F.level_sn + L.first;
             cudaStream_t st = sv[br++];
-            if (L.kind == 2) {
+            if (L.kind == 3) { k_single_check<<<cdiv(L.count, 256), 256, 0, st>>>(A, list, L.count); launches++; }
+            else if (L.kind == 2) {
                 {
                     cudaLaunchConfig_t cfg = {};
                     cfg.gridDim = dim3(L.count, cdiv(L.maxN, CW)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = st;
@@ -1472,13 +1495,15 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
         for (int t = 0; t < S->nlevel; t++) {
             int lv = pass == 0 ? t : S->nlevel - 1 - t;
             int b = S->level_ptr[lv], e = S->level_ptr[lv + 1], q = b;
+            const int nsing = lv == 0 ? F.nsing : 0;              // singleton leaf fronts: one division forward, nothing backward
+            e -= nsing;
             while (q < e && ordN(q) > SOLVE_WARP_N) q++;
             // fronts wider than SOLVE_BIG_N rows get 1024 threads (one panel row / one panel column per
             // thread / warp), the rest of the CTA-solved fronts 256, fronts up to SOLVE_WARP_N one warp: up to three
             // independent launches per level, each on its own branch
             int qb = b;
             while (qb < q && ordN(qb) > SOLVE_BIG_N) qb++;
-            const int nbranch = (qb > b) + (q > qb) + (e > q);
+            const int nbranch = (qb > b) + (q > qb) + (e > q) + (nsing && pass == 0);
             cudaStream_t sv[4];
             fork_level(d, nbranch, sv);
             int br = 0;
@@ -1509,6 +1534,7 @@ static long issue_solve_args(qpdo_dev *d, const SArgs &A)
                 else k_bwd<32><<<e - q, 32, sizeof(double) * (Nm + 2 + NB * Nm), st>>>(A, F.level_sn + q);
                 launches++;
             }
+            if (nsing && pass == 0) { k_single_fwd<<<cdiv(nsing, 256), 256, 0, sv[br++]>>>(A, F.level_sn + e, nsing); launches++; }
             join_level(d, nbranch, sv);
         }
     return launches;

@@ -205,6 +205,33 @@ def test_factor_solve_is_deterministic_across_repeats_and_stream_modes(cuda_lib,
         assert np.array_equal(x, xs[0])
 
 
+def test_singleton_leaf_fronts_elementwise_path_is_bit_identical(cuda_lib, monkeypatch):
+    """Columns of K without off-diagonal entries (nearly all of a Lasso-type problem with few weighted rows) are handled by
+    element-wise kernels instead of one CTA per front (QPDO_B200_SINGLETONS=0 switches that off): same x, bit for bit."""
+    import qpdo_b200
+    p = problems.lasso_dual(6000, 3000, window=200)
+    rng = np.random.default_rng(11)
+    xs = []
+    for mode in ("1", "0"):
+        monkeypatch.setenv("QPDO_B200_SINGLETONS", mode)
+        monkeypatch.setenv("QPDO_PATTERN", "dynamic")       # pattern = the weighted rows only: most columns are isolated
+        s = qpdo_b200.QPDO()
+        s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0))
+        n, m = s.n, s.m
+        if not xs:
+            om = np.zeros(m); om[rng.choice(m, 40, replace=False)] = rng.random(40) * 5
+            b = rng.standard_normal(n)
+        f, t = C.c_float(), C.c_float()
+        x = np.zeros(n)
+        assert cuda_lib.qpdo_dev_test_factor_solve(s.device, om.ctypes.data_as(_pd), 1e-3, b.ctypes.data_as(_pd), x.ctypes.data_as(_pd),
+                                                   C.byref(f), C.byref(t)) == 0, cuda_lib.qpdo_dev_last_error()
+        info = capi.DevSymbolicInfo(); cuda_lib.qpdo_dev_get_symbolic_info(s.device, C.byref(info))
+        assert info.nsuper > 4000                            # thousands of one-pivot fronts
+        xs.append(x)
+        s.delete()
+    assert np.isfinite(xs[0]).all() and np.array_equal(xs[0], xs[1])
+
+
 def test_full_size_cont300_against_reference_golden(cuda_lib):
     """BASELINE config 3 at full size (n = 90,300, m = 180,300) against the unmodified reference's
     result (tests/golden/cont300.npz, make_golden_large.py) + KKT conditions recomputed on the host."""
