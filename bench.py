@@ -593,6 +593,7 @@ def run_c4(args, dist):
         steps = c4_path(s, p, npath)
     dist.barrier()
     lib.qpdo_dev_get_profile(s.device, C.byref(prof), 1)
+    sinfo = capi.DevSymbolicInfo(); lib.qpdo_dev_get_symbolic_info(s.device, C.byref(sinfo))
     s.delete()
     newton = max(1, prof.n_newton)
     path_s = sum(t for t, _, _, _ in steps)
@@ -604,6 +605,7 @@ def run_c4(args, dist):
                                    "%d-step path (the path is sequential: one run, no warm-up; A and L exceed L2)" % npath, "n": n, "m": m, "nnzA": int(p["A"].nnz)},
             "path_seconds": worst[1], "setup_s": setup_s, "path_iterations": [it for _, it, _, _ in steps], "path_status": [st for _, _, st, _ in steps],
             "newton_steps": int(prof.n_newton),
+            "host_analysis_seconds": float(sinfo.analyze_seconds),   # symbolic (re-)analyses on the support-following pattern, all of setup + path
             "phases_ms_per_newton": {"assemble": prof.assemble_ms / newton, "factor": prof.factor_ms / newton, "solve": prof.solve_ms / newton,
                                      "spmv": prof.spmv_ms / newton, "linesearch": prof.linesearch_ms / newton},
             "roofline": {"bound": "hbm", "kernel": "k_spmv_rows (A x, A' y; the active-set factor is tiny on this path)",

@@ -50,6 +50,8 @@ struct Factor {
     // pattern management (factor.cu): row set P of A that the current symbolic structure covers
     std::vector<int> hQp, hQi, hAp, hAi;          // host copies of the patterns
     std::vector<void *> owned;                    // device arrays that depend on the pattern
+    std::vector<unsigned char> hP;                // host copy of the current pattern row set (empty: superset)
+    bool headroom = true;                         // new row sets keep the old rows and take in the rows nearest to a bound
     unsigned char *inP = nullptr;                 // [m] row is in P
     int *cnt = nullptr, *cnt_host = nullptr;      // support / outside counters
     int ordering = 1, npattern = 0, analyses = 0;

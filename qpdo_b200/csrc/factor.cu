@@ -1272,6 +1272,7 @@ int factor_setup(qpdo_dev *d, int ordering)
     if (cudaEventCreateWithFlags(&F.ev_fork, cudaEventDisableTiming) != cudaSuccess) { qpdo_set_error("factor_setup: event creation failed"); return -1; }
     { const char *cv = getenv("QPDO_B200_CONCURRENT"); F.concurrent = !(cv && !strcmp(cv, "0")); }
     { const char *pv = getenv("QPDO_B200_PDL"); F.pdl = !(pv && !strcmp(pv, "0")); }                           // 0: plain stream order between panel steps (A/B)
+    { const char *hv = getenv("QPDO_B200_PATTERN_HEADROOM"); F.headroom = !(hv && !strcmp(hv, "0")); }
     { const char *nv = getenv("QPDO_B200_SINGLETONS"); F.no_singletons = nv && !strcmp(nv, "0"); }             // 0: singleton fronts through the per-front kernels (A/B)
     { const char *sv = getenv("QPDO_B200_SOLVE"); F.solve_cluster = !(sv && !strcmp(sv, "cta")); }   // "cta": one CTA per big front (A/B)
     cudaFuncSetAttribute(k_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -1314,9 +1315,12 @@ static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
         pAp = Ap.data(); pAi = Ai.data();
     }
     F.full = (rowmask == nullptr); F.npattern = mr;
+    if (rowmask) F.hP.assign(rowmask, rowmask + m); else F.hP.clear();
     char err[256];
+    auto t_sym0 = std::chrono::steady_clock::now();
     qpdo_symbolic *S = qpdo_symbolic_analyze(n, mr, F.hQp.data(), F.hQi.data(), pAp, pAi, F.ordering, err);
     if (!S) { qpdo_set_error("symbolic analysis failed: %s", err); return -1; }
+    const double sym_ms = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_sym0).count() * 1e3;
     if (rowmask) {                                        // back to the numbering of the full A
         for (int64_t t = 0; t < S->ntriple; t++) { S->Kt_row[t] = rowmap[S->Kt_row[t]]; S->Kt_a1[t] = nzmap[S->Kt_a1[t]]; S->Kt_a2[t] = nzmap[S->Kt_a2[t]]; }
     }
@@ -1378,7 +1382,11 @@ static int factor_analyze(qpdo_dev *d, const unsigned char *rowmask)
             }
         }
     }
-    d->analyze_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    const double all_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    d->analyze_seconds += all_s;
+    if (getenv("QPDO_B200_TRACE_ANALYZE"))                // one line per (re-)analysis: pattern rows, supernodes, host symbolic ms, total ms
+        fprintf(stderr, "qpdo_b200: analysis %d: %d pattern rows%s, %d supernodes, symbolic %.1f ms, with release / upload %.1f ms\n",
+                F.analyses, mr, rowmask ? "" : " (superset)", ns, sym_ms, all_s * 1e3);
     return factor_refresh_products(d);
 }
 
@@ -1400,6 +1408,33 @@ static int factor_ensure_pattern(qpdo_dev *d)
     CUDA_OK(cudaStreamSynchronize(d->st));
     std::vector<unsigned char> mask((size_t)m);
     for (int i = 0; i < m; i++) mask[i] = om[i] != 0.0;
+    // Headroom (QPDO_B200_PATTERN_HEADROOM=0 switches it off): a pattern that is exactly the support is invalid again as soon as
+    // the next row enters -- along a regularisation path that is every other Newton step (C4: 25 analyses of ~46 ms = 3/4 of
+    // the path).  So the new row set also keeps the rows of the previous one, and takes in the inactive rows nearest to a
+    // bound (smallest min(w - l, u - w)), half as many as the support: the rows most likely to enter next.  Rows with zero
+    // weight only add structural zeros to K; the 4x rule above sheds them again.
+    if (F.headroom) {
+        const int budget = 2 * support + 2048;                 // well inside the 4 * support + 4096 of the shrink rule
+        int have = support;
+        if (!F.hP.empty())
+            for (int i = 0; i < m && have < budget; i++) if (F.hP[i] && !mask[i]) { mask[i] = 1; have++; }
+        const int want = std::min(budget - have, std::max(32, support / 2));
+        if (want > 0) {
+            std::vector<double> w((size_t)m), lo((size_t)m), up((size_t)m);
+            CUDA_OK(cudaMemcpyAsync(w.data(), d->w, sizeof(double) * m, cudaMemcpyDeviceToHost, d->st));
+            CUDA_OK(cudaMemcpyAsync(lo.data(), d->l, sizeof(double) * m, cudaMemcpyDeviceToHost, d->st));
+            CUDA_OK(cudaMemcpyAsync(up.data(), d->u, sizeof(double) * m, cudaMemcpyDeviceToHost, d->st));
+            CUDA_OK(cudaStreamSynchronize(d->st));
+            std::vector<std::pair<double, int>> cand;
+            for (int i = 0; i < m; i++)
+                if (!mask[i]) { const double sl = std::min(w[i] - lo[i], up[i] - w[i]); if (sl == sl && sl < 1e300) cand.push_back(std::make_pair(sl, i)); }
+            const size_t take = std::min(cand.size(), (size_t)want);
+            if (take) {
+                std::nth_element(cand.begin(), cand.begin() + (take - 1), cand.end());
+                for (size_t t = 0; t < take; t++) mask[cand[t].second] = 1;
+            }
+        }
+    }
     return factor_analyze(d, mask.data());
 }
 
