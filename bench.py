@@ -583,6 +583,10 @@ def run_c4(args, dist):
     p = c4_problem(args)
     n, m = p["q"].size, p["A"].shape[0]
     npath = len(p["lams"])
+    # the path is one sequential run without warm-up steps: create the CUDA context with a throwaway tiny QP first, so that the
+    # timed qpdo_setup is the setup of this problem and not the first CUDA call of the process (c3 / c1 time theirs warm too)
+    from qpdo_b200 import problems as _pr
+    _w = _pr.random_qp(40, 20, 0.2, seed=1); _s = qpdo_b200.QPDO(); _s.setup(_w["Q"], _w["q"], _w["A"], _w["l"], _w["u"], dict(verbose=0)); _s.solve(); _s.delete()
     s = qpdo_b200.QPDO()
     t0 = time.perf_counter(); s.setup(p["Q"], p["q"], p["A"], p["l"], p["u"], dict(verbose=0)); setup_s = time.perf_counter() - t0
     prof = capi.DevProfile()
