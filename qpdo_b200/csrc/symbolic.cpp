@@ -37,9 +37,9 @@ extern "C" void qpdo_symbolic_free(qpdo_symbolic *S)
     free(S);
 }
 
-extern "C" qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, const int *Qi,
-                                                const int *Ap, const int *Ai, int ordering,
-                                                char *err)
+static qpdo_symbolic *analyze_full(int n, int m, const int *Qp, const int *Qi,
+                                   const int *Ap, const int *Ai, int ordering,
+                                   char *err)
 {
     if (err) err[0] = 0;
     // ------------------------------------------------------------------ CSR pattern of A
@@ -383,5 +383,106 @@ extern "C" qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, con
     S->lnz = 0; S->flops = 0;
     for (int j = 0; j < n; j++) { S->lnz += cc[j]; S->flops += (double)cc[j] * (double)cc[j]; }
     S->lnz_stored = Lp[ns]; S->usize = Up[ns]; S->max_front = max_front; S->max_nc = max_nc;
+    return S;
+}
+
+// ------------------------------------------------------------------------------------------------ singleton columns
+// A column of K without off-diagonal entries (no off-diagonal of Q, and every row of A that touches it touches nothing
+// else) is a front of its own: one pivot, no rows below, no children, no parent.  With a support-following pattern
+// (factor.cu, Lasso-type problems) these are nearly all of n, and pushing them through ordering, tree, counts and
+// supernodes is most of an analysis (33 ms at n = 200k, 11 times along the C4 path).  So: analyse the subproblem on the
+// other columns with the code above (order-preserving relabelling: every tie-break falls the same way, the elimination
+// order of every connected component is the one the full analysis produces), then append the singletons -- permuted
+// columns nsub .. n-1, supernodes of their own at the tail of level 0, one K entry each (the diagonal, with the products
+// a_rj^2 of its column of A).
+namespace {
+template <class T> bool grow(T *&p, size_t newn)
+{
+    T *q = (T *)realloc(p, sizeof(T) * (newn ? newn : 1));
+    if (!q) return false;
+    p = q;
+    return true;
+}
+}
+
+extern "C" qpdo_symbolic *qpdo_symbolic_analyze(int n, int m, const int *Qp, const int *Qi,
+                                                const int *Ap, const int *Ai, int ordering,
+                                                char *err)
+{
+    if (err) err[0] = 0;
+    { const char *ev = getenv("QPDO_SYM_COMPRESS"); if ((ev && !strcmp(ev, "0")) || n < 4096 || ordering == 0) return analyze_full(n, m, Qp, Qi, Ap, Ai, ordering, err); }
+    // ---- which columns have an off-diagonal entry in K?
+    std::vector<unsigned char> coupled((size_t)n, 0);
+    for (int c = 0; c < n; c++)
+        for (int k = Qp[c]; k < Qp[c + 1]; k++) if (Qi[k] != c) { coupled[c] = 1; coupled[Qi[k]] = 1; }
+    {
+        std::vector<int> rowcnt((size_t)std::max(m, 1), 0);
+        for (int k = 0; k < Ap[n]; k++) rowcnt[Ai[k]]++;
+        for (int c = 0; c < n; c++)
+            for (int k = Ap[c]; k < Ap[c + 1]; k++) if (rowcnt[Ai[k]] >= 2) { coupled[c] = 1; break; }
+    }
+    int nsub = 0;
+    for (int c = 0; c < n; c++) nsub += coupled[c];
+    const int nsing = n - nsub;
+    if (nsing < n / 2 || nsub == 0) return analyze_full(n, m, Qp, Qi, Ap, Ai, ordering, err);
+    // ---- the subproblem: columns (and Q rows) relabelled in ascending order, positions of the kept entries remembered
+    std::vector<int> subid((size_t)n, -1), subv((size_t)nsub), singv((size_t)nsing);
+    for (int c = 0, a = 0, b = 0; c < n; c++) { if (coupled[c]) { subid[c] = a; subv[a++] = c; } else singv[b++] = c; }
+    std::vector<int> sQp((size_t)nsub + 1, 0), sQi, qmap, sAp((size_t)nsub + 1, 0), sAi, amap;
+    for (int a = 0; a < nsub; a++) {
+        const int c = subv[a];
+        for (int k = Qp[c]; k < Qp[c + 1]; k++) { sQi.push_back(subid[Qi[k]]); qmap.push_back(k); }     // rows of a coupled column are coupled or the diagonal
+        sQp[a + 1] = (int)sQi.size();
+        for (int k = Ap[c]; k < Ap[c + 1]; k++) { sAi.push_back(Ai[k]); amap.push_back(k); }
+        sAp[a + 1] = (int)sAi.size();
+    }
+    if (sQi.empty()) sQi.push_back(0);
+    if (sAi.empty()) sAi.push_back(0);
+    qpdo_symbolic *S = analyze_full(nsub, m, sQp.data(), sQi.data(), sAp.data(), sAi.data(), ordering, err);
+    if (!S) return NULL;
+    // ---- back to the caller's numbering: columns, positions in Q and A
+    const int ns0 = S->nsuper, ns = ns0 + nsing;
+    const int64_t nnzK0 = S->nnzK, nt0 = S->ntriple, nrows0 = S->sn_rowptr[ns0];
+    for (int64_t e = 0; e < nnzK0; e++) if (S->Kq[e] >= 0) S->Kq[e] = qmap[S->Kq[e]];
+    for (int64_t t = 0; t < nt0; t++) { S->Kt_a1[t] = amap[S->Kt_a1[t]]; S->Kt_a2[t] = amap[S->Kt_a2[t]]; }
+    int64_t nt_sing = 0;
+    for (int t = 0; t < nsing; t++) nt_sing += Ap[singv[t] + 1] - Ap[singv[t]];
+    const int64_t nnzK = nnzK0 + nsing, ntriple = nt0 + nt_sing;
+    bool ok = grow(S->perm, n) && grow(S->pinv, n) && grow(S->col2sn, n) && grow(S->Kp, (size_t)n + 1) &&
+              grow(S->sn_start, (size_t)ns + 1) && grow(S->sn_nr, ns) && grow(S->sn_rowptr, (size_t)ns + 1) && grow(S->sn_parent, ns) &&
+              grow(S->child_ptr, (size_t)ns + 1) && grow(S->child_idx, ns) && grow(S->Lp, (size_t)ns + 1) && grow(S->Up, (size_t)ns + 1) &&
+              grow(S->sn_level, ns) && grow(S->level_sn, ns) && grow(S->Ki, nnzK) && grow(S->Kdst, nnzK) && grow(S->Kq, nnzK) &&
+              grow(S->Ktp, (size_t)nnzK + 1) && grow(S->Kt_row, ntriple) && grow(S->Kt_a1, ntriple) && grow(S->Kt_a2, ntriple);
+    if (!ok) { qpdo_symbolic_free(S); if (err) snprintf(err, 256, "symbolic: out of memory"); return NULL; }
+    // permutation: perm[new] = old; the subproblem's columns first, then the singletons in ascending order
+    for (int a = 0; a < nsub; a++) S->perm[a] = subv[S->perm[a]];
+    for (int t = 0; t < nsing; t++) S->perm[nsub + t] = singv[t];
+    for (int k = 0; k < n; k++) S->pinv[S->perm[k]] = k;
+    // level lists: the singletons go to the tail of level 0 (fronts of a level are sorted by decreasing order)
+    {
+        const int l0e = S->level_ptr[1];
+        memmove(S->level_sn + l0e + nsing, S->level_sn + l0e, sizeof(int) * (size_t)(ns0 - l0e));
+        for (int t = 0; t < nsing; t++) S->level_sn[l0e + t] = ns0 + t;
+        for (int lv = 1; lv <= S->nlevel; lv++) S->level_ptr[lv] += nsing;
+    }
+    int64_t tpos = nt0;
+    for (int t = 0; t < nsing; t++) {
+        const int s = ns0 + t, col = nsub + t, c = singv[t];
+        S->sn_start[s + 1] = col + 1;                      // (sn_start[ns0] == nsub already)
+        S->sn_nr[s] = 0; S->sn_rowptr[s + 1] = nrows0; S->sn_parent[s] = -1;
+        S->child_ptr[s + 1] = S->child_ptr[ns0];
+        S->Lp[s + 1] = S->Lp[s] + 1; S->Up[s + 1] = S->Up[s];
+        S->sn_level[s] = 0; S->col2sn[col] = s;
+        const int64_t e = nnzK0 + t;
+        S->Kp[col + 1] = (int)(e + 1);
+        S->Ki[e] = col; S->Kdst[e] = S->Lp[s];
+        S->Kq[e] = (Qp[c + 1] > Qp[c]) ? Qp[c] : -1;       // an uncoupled column of Q holds its diagonal entry or nothing
+        for (int k = Ap[c]; k < Ap[c + 1]; k++) { S->Kt_row[tpos] = Ai[k]; S->Kt_a1[tpos] = k; S->Kt_a2[tpos] = k; tpos++; }
+        S->Ktp[e + 1] = tpos;
+    }
+    S->n = n; S->nsuper = ns; S->nnzK = nnzK; S->ntriple = ntriple;
+    S->lnz += nsing; S->flops += (double)nsing; S->lnz_stored = S->Lp[ns]; S->usize = S->Up[ns];
+    if (S->max_front < 1) S->max_front = 1;
+    if (S->max_nc < 1) S->max_nc = 1;
     return S;
 }
