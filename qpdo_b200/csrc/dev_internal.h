@@ -49,7 +49,8 @@ struct Factor {
     long launches_factor = 0, launches_solve = 0;
     // pattern management (factor.cu): row set P of A that the current symbolic structure covers
     std::vector<int> hQp, hQi, hAp, hAi;          // host copies of the patterns
-    std::vector<void *> owned;                    // device arrays that depend on the pattern
+    std::vector<std::pair<void *, size_t>> pool;  // device arrays that depend on the pattern: slot pool (pointer, capacity in bytes)
+    size_t pool_next = 0;                         // next slot of the running analysis
     std::vector<unsigned char> hP;                // host copy of the current pattern row set (empty: superset)
     bool headroom = true;                         // new row sets keep the old rows and take in the rows nearest to a bound
     unsigned char *inP = nullptr;                 // [m] row is in P

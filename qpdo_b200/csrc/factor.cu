@@ -1220,8 +1220,40 @@ static SArgs sargs(qpdo_dev *d)
 static const int DYNAMIC_MIN_ROWS = 20000;                // smaller problems always use the superset
 static const int FULL_FRACTION = 8;                       // support > m / FULL_FRACTION: superset from then on
 
-template <class T> static int f_alloc(qpdo_dev *d, T **p, size_t count) { if (dev_alloc(d, p, count)) return -1; d->F.owned.push_back((void *)*p); return 0; }
-template <class T> static int f_upload(qpdo_dev *d, T **p, const T *h, size_t count) { if (dev_upload(d, p, h, count)) return -1; d->F.owned.push_back((void *)*p); return 0; }
+// Device arrays that depend on the pattern come from a slot pool: an analysis asks for them in the same order every time, a
+// slot is reused when it is large enough (zero-filled like a fresh allocation) and replaced with 25 % headroom otherwise.
+// A support-following pattern is re-analysed a dozen times along a regularisation path; freeing and allocating ~27 arrays
+// each time was a third of the cost of an analysis.  The buffers stay registered in d->allocs until the context is destroyed.
+static int pool_get(qpdo_dev *d, void **out, size_t bytes)
+{
+    Factor &F = d->F;
+    if (!bytes) bytes = 8;
+    const size_t slot = F.pool_next++;
+    if (slot >= F.pool.size()) F.pool.push_back(std::make_pair((void *)nullptr, (size_t)0));
+    if (F.pool[slot].second < bytes) {
+        if (F.pool[slot].first) {
+            void *q = F.pool[slot].first;
+            for (size_t i = 0; i < d->allocs.size(); i++) if (d->allocs[i] == q) { d->allocs[i] = d->allocs.back(); d->allocs.pop_back(); break; }
+            cudaFree(q);
+        }
+        const size_t cap = bytes + bytes / 4;
+        void *v = nullptr;
+        cudaError_t e = cudaMalloc(&v, cap);
+        if (e != cudaSuccess) { F.pool[slot] = std::make_pair((void *)nullptr, (size_t)0); qpdo_set_error("cudaMalloc(%zu): %s", cap, cudaGetErrorString(e)); return -1; }
+        d->allocs.push_back(v);
+        F.pool[slot] = std::make_pair(v, cap);
+    }
+    CUDA_OK(cudaMemsetAsync(F.pool[slot].first, 0, bytes, d->st));
+    *out = F.pool[slot].first;
+    return 0;
+}
+template <class T> static int f_alloc(qpdo_dev *d, T **p, size_t count) { void *v; if (pool_get(d, &v, sizeof(T) * count)) return -1; *p = (T *)v; return 0; }
+template <class T> static int f_upload(qpdo_dev *d, T **p, const T *h, size_t count)
+{
+    if (f_alloc(d, p, count)) return -1;
+    if (count) CUDA_OK(cudaMemcpyAsync(*p, h, sizeof(T) * count, cudaMemcpyHostToDevice, d->st));
+    return 0;
+}
 static void factor_release(qpdo_dev *d)
 {
     Factor &F = d->F;
@@ -1229,11 +1261,7 @@ static void factor_release(qpdo_dev *d)
     if (F.g_factor) cudaGraphExecDestroy(F.g_factor);
     if (F.g_solve) cudaGraphExecDestroy(F.g_solve);
     F.g_factor = F.g_solve = nullptr;
-    for (void *q : F.owned) {
-        for (size_t i = 0; i < d->allocs.size(); i++) if (d->allocs[i] == q) { d->allocs[i] = d->allocs.back(); d->allocs.pop_back(); break; }
-        cudaFree(q);
-    }
-    F.owned.clear();
+    F.pool_next = 0;                                      // the next analysis reuses the slots
     if (F.S) qpdo_symbolic_free(F.S);
     F.S = nullptr;
 }
