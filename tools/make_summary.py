@@ -51,7 +51,8 @@ o.append("## C1 (n = 1000, m = 500) and C4 (Lasso path, n = 200k, m = 100k)\n")
 o.append("| | start of round 2 | HEAD | reference, same box |\n|---|---|---|---|")
 o.append("| C1 ms per cold solve (33 passes) | 32.1 | **%.1f** | %.1f |" % (c1["value"], c1["cpu_baseline"]["value"]))
 o.append("| C1 KKT ms per Newton step | 1.02 | %.2f | |" % c1["kkt_ms_per_newton"])
-o.append("| C4 seconds for the 20-step path (of which %.2f s host re-analysis: 11 analyses with the headroom rule, 25 without; one run on a slower host: 1.49 s) | 5.19 | **%.2f** | %.2f |" % (c4["host_analysis_seconds"], c4["path_seconds"], c4["cpu_baseline"]["path_seconds"]))
-o.append("| C4 KKT ms per Newton step (singleton leaf fronts element-wise: 0.85 -> 0.14 before the headroom rows) | 0.49 | %.2f | |" % c4["value"])
+o.append("| C4 seconds for the 20-step path (of which %.2f s host re-analysis; 0.44 - 0.54 s between boxes) | 5.19 | **%.2f** | %.2f |" % (c4["host_analysis_seconds"], c4["path_seconds"], c4["cpu_baseline"]["path_seconds"]))
+o.append("| C4 KKT ms per Newton step | 0.49 | %.2f | |" % c4["value"])
+o.append("\nC4 in steps (path seconds, same iteration counts throughout): 5.19 at the start of the round; 1.5 - 2.3 with the kernels of this round (25 re-analyses of ~46 ms on the host dominate); singleton leaf fronts element-wise (KKT per Newton step 0.85 -> 0.14 ms); 0.83 with headroom in the pattern row set (11 analyses); 0.54 with the singleton columns left out of the symbolic analysis (38 -> 8 ms per analysis); 0.44 with pooled device arrays.\n")
 open(os.path.join(P, "r2_summary.md"), "w").write("\n".join(o) + "\n")
 print("written", os.path.join(P, "r2_summary.md"))
