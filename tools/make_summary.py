@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""tools/make_summary.py -- profiles/r2_summary.md from the committed bench lines (profiles/r2e: lines at the round's HEAD,
+"""tools/make_summary.py -- profiles/r2_summary.md from the committed bench lines (profiles/r2f: lines at the round's HEAD,
 profiles/r2c: scaling lines r2d_* and the ncu tables) and the ncu records profiles/c5_ncu.json / c3_ncu.json."""
 import json
 import os
@@ -11,12 +11,12 @@ def L(d, f):
     return json.loads(open(os.path.join(P, d, f)).read().strip().splitlines()[-1])
 
 
-c5 = L("r2e", "r2e_bench_c5.json"); k = c5["kkt"]; c1 = L("r2e", "r2e_bench_c1.json"); c4 = L("r2e", "r2e_bench_c4.json"); c3 = L("r2e", "r2e_bench_c3.json")
+c5 = L("r2f", "r2f_bench_c5.json"); k = c5["kkt"]; c1 = L("r2f", "r2f_bench_c1.json"); c4 = L("r2f", "r2f_bench_c4.json"); c3 = L("r2f", "r2f_bench_c3.json")
 ncu5 = json.load(open(os.path.join(P, "c5_ncu.json")))
 sc = {N: L("r2c", "r2d_bench_c5_%dgpu.json" % N) for N in (1, 2, 4, 8)}
 o = []
 o.append("# Round 2 on one B200 (and 2 / 4 / 8): what was measured, where the records are\n")
-o.append("Bench lines at the round's HEAD: `profiles/r2e/` (GPU tests 63 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables: `profiles/r2c/` (commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
+o.append("Bench lines at the round's HEAD: `profiles/r2f/` (an earlier set: `profiles/r2e/`) (GPU tests 63 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables: `profiles/r2c/` (commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
 o.append("## C5: 65,536 MPC QPs (n = 100, m = 150)\n")
 o.append("| | round 1 | round 2 |\n|---|---|---|")
 o.append("| QP/s, inputs resident in HBM | 798k | **%.0fk** |" % (c5["value"] / 1e3))
@@ -51,7 +51,7 @@ o.append("## C1 (n = 1000, m = 500) and C4 (Lasso path, n = 200k, m = 100k)\n")
 o.append("| | start of round 2 | HEAD | reference, same box |\n|---|---|---|---|")
 o.append("| C1 ms per cold solve (33 passes) | 32.1 | **%.1f** | %.1f |" % (c1["value"], c1["cpu_baseline"]["value"]))
 o.append("| C1 KKT ms per Newton step | 1.02 | %.2f | |" % c1["kkt_ms_per_newton"])
-o.append("| C4 seconds for the 20-step path (of which %.2f s host re-analysis; 0.44 - 0.54 s between boxes) | 5.19 | **%.2f** | %.2f |" % (c4["host_analysis_seconds"], c4["path_seconds"], c4["cpu_baseline"]["path_seconds"]))
+o.append("| C4 seconds for the 20-step path (of which %.2f s host re-analysis; 0.44 - 0.61 s between boxes) | 5.19 | **%.2f** | %.2f |" % (c4["host_analysis_seconds"], c4["path_seconds"], c4["cpu_baseline"]["path_seconds"]))
 o.append("| C4 KKT ms per Newton step | 0.49 | %.2f | |" % c4["value"])
 o.append("\nC4 in steps (path seconds, same iteration counts throughout): 5.19 at the start of the round; 1.5 - 2.3 with the kernels of this round (25 re-analyses of ~46 ms on the host dominate); singleton leaf fronts element-wise (KKT per Newton step 0.85 -> 0.14 ms); 0.83 with headroom in the pattern row set (11 analyses); 0.54 with the singleton columns left out of the symbolic analysis (38 -> 8 ms per analysis); 0.44 with pooled device arrays.\n")
 open(os.path.join(P, "r2_summary.md"), "w").write("\n".join(o) + "\n")
