@@ -16,7 +16,7 @@ ncu5 = json.load(open(os.path.join(P, "c5_ncu.json")))
 sc = {N: L("r2c", "r2d_bench_c5_%dgpu.json" % N) for N in (1, 2, 4, 8)}
 o = []
 o.append("# Round 2 on one B200 (and 2 / 4 / 8): what was measured, where the records are\n")
-o.append("Bench lines at the round's HEAD: `profiles/r2f/` (an earlier set: `profiles/r2e/`) (GPU tests 63 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables: `profiles/r2c/` (commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
+o.append("Bench lines at the round's HEAD: `profiles/r2f/` (an earlier set: `profiles/r2e/`) (GPU tests 64 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables: `profiles/r2c/` (commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
 o.append("## C5: 65,536 MPC QPs (n = 100, m = 150)\n")
 o.append("| | round 1 | round 2 |\n|---|---|---|")
 o.append("| QP/s, inputs resident in HBM | 798k | **%.0fk** |" % (c5["value"] / 1e3))
@@ -35,7 +35,7 @@ for N in (1, 2, 4, 8):
     d = sc[N]
     o.append("| %d | %.3fM | %.3f | %.3fM | %.3f | %.2f / %.2f |" % (N, d["value"] / 1e6, d["value"] / b["value"] / N, d["e2e"]["value"] / 1e6, d["e2e"]["value"] / b["e2e"]["value"] / N, d["kernel_ms_per_step"], d["kernel_ms_natural_order"]))
 o.append("\nRound 1: 0.98 / 0.95 / 0.83 (value), 0.98 / 0.90 / 0.71 (end to end).  The end-to-end step at 8 GPUs is bound by the HOST: the ranks together move 727 MB of inputs and 144 MB of results per step through host memory and PCIe (68 GB/s aggregate at the observed 12.8 ms); the same 8,192-QP share on ONE GPU of the box has 0.77 ms of overhead over its 8.37 ms kernel (0.92; `QPDO_BATCH_CHUNKS` 2 / default 4 / 8: 9.58 / 9.14 / 10.91 ms).\n")
-o.append("## C3: CONT-300-shaped QP (n = 90,300, m = 180,300): the `kkt` key of the default line and `r2e_bench_c3.json`\n")
+o.append("## C3: CONT-300-shaped QP (n = 90,300, m = 180,300): the `kkt` key of the default line and `r2f_bench_c3.json`\n")
 ph = k["phases_ms_per_newton"]
 o.append("| ms per Newton step | round 1 | start of round 2 | HEAD |\n|---|---|---|---|")
 o.append("| K assembly | 0.04 | 0.04 | %.2f |" % ph["assemble"])
