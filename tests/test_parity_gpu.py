@@ -177,12 +177,15 @@ def test_factor_solve_residual(cuda_lib, gen):
     s.delete()
 
 
-def test_factor_solve_is_deterministic_across_repeats_and_stream_modes(cuda_lib, monkeypatch):
+@pytest.mark.parametrize("gen", ["cont100", "c1"])
+def test_factor_solve_is_deterministic_across_repeats_and_stream_modes(cuda_lib, monkeypatch, gen):
     """The same factorization + solve, 12 times over, and once more with the independent launches of a tree level on ONE
     stream (QPDO_B200_CONCURRENT=0), and with the one-CTA solves of the big fronts (QPDO_B200_SOLVE=cta): every x bit-identical.  A race between warps of a front kernel or between the
     concurrent branches of the captured graphs shows up here as a differing bit."""
     import qpdo_b200
-    p = problems.cont_like(100)                   # 1,013 fronts: every size bucket and the blocked path
+    # cont100: 1,013 fronts, every size bucket and the blocked path; c1: a dense 815-row root front (26 panel steps chained by
+    # programmatic dependent launch, 26-step cluster solves)
+    p = problems.cont_like(100) if gen == "cont100" else problems.random_qp(1000, 500, 0.01, seed=1)
     rng = np.random.default_rng(7)
     xs = []
     for mode in ("1", "0", "cta"):                # "cta": big fronts solved by one CTA each instead of a cluster (same bits by design)
