@@ -149,41 +149,57 @@ struct ResArgs {
     double *res_prim, *res_prim_in, *w, *df, *res_dual, *res_dual_in;
     qpdo_dev_scalars *sc;
 };
-__global__ void k_residuals(ResArgs A)
+// one constraint row of the residual block (iteration.c:38-46, 75-81): same statements as the scalar kernel of round 1
+__device__ __forceinline__ void res_row(const ResArgs &A, double Ax, double y, double l, double u, double mu, double yb, double E, double Einv,
+                                        double &rp, double &w, double &rpi, double &np, double &npi)
 {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double t;
+    if (A.scaled) { t = E * y; t = t * A.cinv; t = E * t; t = Ax + t; } else t = Ax + y;
+    t = clampd(t, l, u);
+    rp = Ax + (-1.0) * t;
+    w = Ax + mu * (yb - 0.5 * y);
+    const double z = clampd(w, l, u);
+    rpi = Ax + mu * (yb - y) - z;
+    const double a = fabs(A.scaled ? Einv * rp : rp), b = fabs(A.scaled ? Einv * rpi : rpi);
+    np = a > np ? a : np; npi = b > npi ? b : npi;
+}
+// one variable (iteration.c:52, 89)
+__device__ __forceinline__ void res_col(const ResArgs &A, double sigma, double Qx, double q, double x, double xbar, double Aty, double Dinv,
+                                        double &rd, double &dfo, double &rdi, double &nd, double &ndi)
+{
+    double df = Qx + q;
+    if (A.proximal) { rd = df + (-sigma) * x; rd = rd + Aty; } else rd = df + Aty;
+    if (A.proximal) df = df + (-sigma) * xbar;
+    dfo = df;
+    rdi = df + Aty;
+    const double a = fabs(A.scaled ? Dinv * rd : rd), b = fabs(A.scaled ? Dinv * rdi : rdi);
+    nd = a > nd ? a : nd; ndi = b > ndi ? b : ndi;
+}
+#define LD2(v, p) do { if (two) v = *reinterpret_cast<const double2 *>((p) + i0); else { v.x = (p)[i0]; v.y = 0.0; } } while (0)
+#define ST2(p, v) do { if (two) *reinterpret_cast<double2 *>((p) + i0) = v; else (p)[i0] = v.x; } while (0)
+__global__ void k_residuals(ResArgs A)
+{   // thread t owns elements 2 t, 2 t + 1 of every vector: 128-bit loads and stores
+    const int i0 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
     double np = 0.0, npi = 0.0, nd = 0.0, ndi = 0.0;
-    if (i < A.m) {
-        double Ax = A.Ax[i], y = A.y[i], l = A.l[i], u = A.u[i], mu = A.mu[i], yb = A.ybar[i];
-        double t;
-        if (A.scaled) {                                   // iteration.c:38-41
-            double E = A.E[i];
-            t = E * y; t = t * A.cinv; t = E * t; t = Ax + t;
-        } else t = Ax + y;
-        t = clampd(t, l, u);
-        double rp = Ax + (-1.0) * t;                       // iteration.c:46
-        A.res_prim[i] = rp;
-        double w = Ax + mu * (yb - 0.5 * y);               // iteration.c:75
-        A.w[i] = w;
-        double z = clampd(w, l, u);
-        double rpi = Ax + mu * (yb - y) - z;               // iteration.c:81
-        A.res_prim_in[i] = rpi;
-        np = fabs(A.scaled ? A.Einv[i] * rp : rp);
-        npi = fabs(A.scaled ? A.Einv[i] * rpi : rpi);
+    if (i0 < A.m) {
+        const bool two = i0 + 1 < A.m;
+        double2 Ax, y, l, u, mu, yb, E = make_double2(1.0, 1.0), Ei = make_double2(1.0, 1.0), rp, w, rpi;
+        LD2(Ax, A.Ax); LD2(y, A.y); LD2(l, A.l); LD2(u, A.u); LD2(mu, A.mu); LD2(yb, A.ybar);
+        if (A.scaled) { LD2(E, A.E); LD2(Ei, A.Einv); }
+        res_row(A, Ax.x, y.x, l.x, u.x, mu.x, yb.x, E.x, Ei.x, rp.x, w.x, rpi.x, np, npi);
+        if (two) res_row(A, Ax.y, y.y, l.y, u.y, mu.y, yb.y, E.y, Ei.y, rp.y, w.y, rpi.y, np, npi);
+        ST2(A.res_prim, rp); ST2(A.w, w); ST2(A.res_prim_in, rpi);
     }
-    if (i < A.n) {
-        double sigma = A.sc->sigma;
-        double df = A.Qx[i] + A.q[i];                      // iteration.c:52
-        double rd;
-        if (A.proximal) { rd = df + (-sigma) * A.x[i]; rd = rd + A.Aty[i]; }
-        else rd = df + A.Aty[i];
-        A.res_dual[i] = rd;
-        if (A.proximal) df = df + (-sigma) * A.xbar[i];    // iteration.c:89
-        A.df[i] = df;
-        double rdi = df + A.Aty[i];
-        A.res_dual_in[i] = rdi;
-        nd = fabs(A.scaled ? A.Dinv[i] * rd : rd);
-        ndi = fabs(A.scaled ? A.Dinv[i] * rdi : rdi);
+    if (i0 < A.n) {
+        const bool two = i0 + 1 < A.n;
+        const double sigma = A.sc->sigma;
+        double2 Qx, q, x = make_double2(0.0, 0.0), xb = make_double2(0.0, 0.0), Aty, Di = make_double2(1.0, 1.0), rd, df, rdi;
+        LD2(Qx, A.Qx); LD2(q, A.q); LD2(Aty, A.Aty);
+        if (A.proximal) { LD2(x, A.x); LD2(xb, A.xbar); }
+        if (A.scaled) LD2(Di, A.Dinv);
+        res_col(A, sigma, Qx.x, q.x, x.x, xb.x, Aty.x, Di.x, rd.x, df.x, rdi.x, nd, ndi);
+        if (two) res_col(A, sigma, Qx.y, q.y, x.y, xb.y, Aty.y, Di.y, rd.y, df.y, rdi.y, nd, ndi);
+        ST2(A.res_dual, rd); ST2(A.df, df); ST2(A.res_dual_in, rdi);
     }
     np = warp_max(np); npi = warp_max(npi); nd = warp_max(nd); ndi = warp_max(ndi);
     if ((threadIdx.x & 31) == 0) {
@@ -259,19 +275,26 @@ __global__ void k_dy_active(const int *act, const double *Adx, const double *mu,
     if (i < m && act[i]) dy[i] = dy[i] + Adx[i] / mu[i];
 }
 struct UpdArgs { int n, m; double *x, *y, *Qx, *Ax, *Aty; const double *dx, *dy, *Qdx, *Adx, *Atdy; const qpdo_dev_scalars *sc; };
+// a[i] += tau * b[i] for elements 2 t, 2 t + 1 (128-bit accesses; the arrays are cudaMalloc'ed one by one: 256-byte aligned)
+__device__ __forceinline__ void axpy2(double *a, const double *b, double tau, int t, int len)
+{
+    const int i = 2 * t;
+    if (i + 1 < len) {
+        double2 x = *reinterpret_cast<double2 *>(a + i);
+        const double2 y = *reinterpret_cast<const double2 *>(b + i);
+        x.x = x.x + tau * y.x; x.y = x.y + tau * y.y;
+        *reinterpret_cast<double2 *>(a + i) = x;
+    } else if (i < len) a[i] = a[i] + tau * b[i];
+}
 __global__ void k_update_iterate(UpdArgs A)
-{   // iteration.c:19-24
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    double tau = A.sc->tau;
-    if (i < A.n) {
-        A.x[i] = A.x[i] + tau * A.dx[i];
-        A.Qx[i] = A.Qx[i] + tau * A.Qdx[i];
-        A.Aty[i] = A.Aty[i] + tau * A.Atdy[i];
-    }
-    if (i < A.m) {
-        A.y[i] = A.y[i] + tau * A.dy[i];
-        A.Ax[i] = A.Ax[i] + tau * A.Adx[i];
-    }
+{   // iteration.c:19-24; thread t owns elements 2 t and 2 t + 1 of every vector
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const double tau = A.sc->tau;
+    axpy2(A.x, A.dx, tau, t, A.n);
+    axpy2(A.Qx, A.Qdx, tau, t, A.n);
+    axpy2(A.Aty, A.Atdy, tau, t, A.n);
+    axpy2(A.y, A.dy, tau, t, A.m);
+    axpy2(A.Ax, A.Adx, tau, t, A.m);
 }
 
 // ---------------------------------------------------------------------------- outer update pieces
@@ -512,7 +535,7 @@ extern "C" int qpdo_dev_residuals(qpdo_dev *d, int proximal, qpdo_dev_scalars *o
         A.res_dual = d->res_dual; A.res_dual_in = d->res_dual_in; A.sc = d->sc;
         CUDA_OK(cudaMemsetAsync(d->sc, 0, 4 * sizeof(double), d->st));
         int N = std::max(d->n, d->m);
-        k_residuals<<<cdiv(N, TPB), TPB, 0, d->st>>>(A);
+        k_residuals<<<cdiv((N + 1) / 2, TPB), TPB, 0, d->st>>>(A);
         if (A.scaled) k_scale_dual_norms<<<1, 1, 0, d->st>>>(d->sc, d->cinv);
         d->prof.n_residual++;
     }
@@ -554,7 +577,7 @@ extern "C" int qpdo_dev_newton_step(qpdo_dev *d, int force_reset, int proximal)
         UpdArgs U;
         U.n = n; U.m = m; U.x = d->x; U.y = d->y; U.Qx = d->Qx_; U.Ax = d->Ax_; U.Aty = d->Aty;
         U.dx = d->dx; U.dy = d->dy; U.Qdx = d->Qdx; U.Adx = d->Adx; U.Atdy = d->Atdy; U.sc = d->sc;
-        k_update_iterate<<<cdiv(std::max(n, m), TPB), TPB, 0, d->st>>>(U);
+        k_update_iterate<<<cdiv((std::max(n, m) + 1) / 2, TPB), TPB, 0, d->st>>>(U);
     }
     d->prof.n_newton++;
     cudaError_t e = cudaGetLastError();
