@@ -65,7 +65,7 @@ int  qpdo_dev_count(void);
 /* qpdo_setup's device half: upload, Ruiz equilibration + cost scaling (scaling.c:24-91 with
  * cholmod_interface.c:162-199 and cholmod_scale.c:137-209), symbolic analysis (replaces
  * cholmod_analyze, cholmod_interface.c:10).  ordering: 0 natural, 1 minimum degree, 2 nested dissection with
- * minimum-degree leaves (the default of qpdo_setup; QPDO_ORDERING=natural|mindeg|nd overrides). */
+ * minimum-degree leaves (the default of qpdo_setup; QPDO_B200_ORDERING=natural|mindeg|nd overrides). */
 int  qpdo_dev_create(qpdo_dev **out, const qpdo_dev_problem *p, int scaling_iters, int ordering,
                      int device);
 void qpdo_dev_destroy(qpdo_dev *d);
