@@ -16,7 +16,7 @@ ncu5 = json.load(open(os.path.join(P, "c5_ncu.json")))
 sc = {N: L("r2c", "r2d_bench_c5_%dgpu.json" % N) for N in (1, 2, 4, 8)}
 o = []
 o.append("# Round 2 on one B200 (and 2 / 4 / 8): what was measured, where the records are\n")
-o.append("Bench lines at the round's HEAD: `profiles/r2f/` (an earlier set: `profiles/r2e/`) (GPU tests 64 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables: `profiles/r2c/` (commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
+o.append("Bench lines at the round's HEAD: `profiles/r2f/` (an earlier set: `profiles/r2e/`) (GPU tests 64 green and `smoke()` in the same call); scaling lines `profiles/r2c/r2d_*`;\nncu launch lists and `--set full` tables at HEAD: `profiles/r2g/` (an earlier set: `profiles/r2c/`, commit af8defb); A/B logs of the individual steps: `profiles/r2b/`; SASS counts per\nkernel: `profiles/r2_sass_counts.txt`.  Clocks 1965 MHz, no throttle reason in any line.\n")
 o.append("## C5: 65,536 MPC QPs (n = 100, m = 150)\n")
 o.append("| | round 1 | round 2 |\n|---|---|---|")
 o.append("| QP/s, inputs resident in HBM | 798k | **%.0fk** |" % (c5["value"] / 1e3))
@@ -27,7 +27,7 @@ o.append("| issue slots busy (ncu) | 33 %% | %.1f %% |" % ncu5["issue_slots_busy
 o.append("| DRAM bytes per QP inside the launch (ncu) / algorithmic | 11.2 KB / 13.3 KB | %.1f KB / 13.3 KB |" % (ncu5["dram_bytes_per_qp"] / 1e3))
 p = c5["parity"]
 o.append("\nParity against the reference, all %d instances, same run: status mismatches %d, iteration mismatches %d (ids %s, deltas %s: the documented knife edges, `profiles/r2_knife_edge.json`), unexplained %s, max relative objective difference %.1e.\n" % (p["instances"], p["status_mismatch"], p["iteration_mismatch"], p["first_ids"], p["iteration_deltas"], p["unexplained"], p["max_rel_objective"]))
-o.append("Batch kernel in round 2 (QP/s at 65,536; each step A/B-checked with `tools/batch_ab.py`): 798k (round 1) -> 864k (four pivots per barrier pair, blocked backward solve) -> 940k (2 x 2 block-pivot reciprocals) -> 964k (an unchanged K is not factored again: 22 % of the Newton steps) -> 990k (one-warp phases as real calls).  Hot lines of the ncu capture: `r2c/r2c_batch_lines.txt`.\n")
+o.append("Batch kernel in round 2 (QP/s at 65,536; each step A/B-checked with `tools/batch_ab.py`): 798k (round 1) -> 864k (four pivots per barrier pair, blocked backward solve) -> 940k (2 x 2 block-pivot reciprocals) -> 964k (an unchanged K is not factored again: 22 % of the Newton steps) -> 990k (one-warp phases as real calls).  Hot lines of the ncu capture: `r2g/r2g_batch_lines.txt`.\n")
 o.append("### Scaling (one 8-GPU box, 65,536 QPs in total)\n")
 o.append("| GPUs | QP/s (HBM-resident) | efficiency | QP/s end to end | efficiency | kernel ms per step (adaptive / natural queue order) |\n|---|---|---|---|---|---|")
 b = sc[1]
@@ -46,7 +46,7 @@ o.append("| exact linesearch | 0.35 | 0.34 | %.2f |" % ph["linesearch"])
 o.append("| whole solve, ms (139 loop passes) | 1,213 | 733 | %.0f |" % c3["ms_per_step"])
 o.append("| reference, same box: ms per loop pass (first 12) | 962 | 976 | %.0f |" % c3["cpu_baseline"]["value"])
 o.append("\nTriangular solves against HBM: %.0f GB/s of algorithmic bytes = %.3f of the measured copy peak (round 1: 0.015); ncu DRAM traffic of the solve launches of one Newton step: %.0f MB (`profiles/c3_ncu.json`).  Factorization against the DMMA peak measured in the run (%.1f TF/s): %.2f TF/s = %.3f.  Host analysis %.2f s (0.24 before the threaded dissection).\n" % (k["roofline"]["achieved"], k["roofline"]["frac"], (k["roofline"].get("traffic") or 0) / 1e6, k["roofline_factor"]["peak"], k["roofline_factor"]["achieved"], k["roofline_factor"]["frac"], k["symbolic"]["analyze_s"]))
-o.append("Steps of the round's second half, factor / solve ms on C3, each with its A/B log: second-generation panel step 3.65 -> 2.72 (`r2b/panel_ab.log`); shared-memory fronts with per-row panel threads 2.72 -> 2.44; forked graph branches per level 2.44 / 1.32 -> 1.78 / 1.07 (`r2b/concurrency_ab.log`); cluster solves of the big fronts 1.07 -> 0.76 (`r2b/cluster_solve_ab.log`); cp.async staging in the small / mid solve kernels 0.77 -> 0.67; programmatic dependent launch along the panel chain 1.75 -> 1.66; per-digit scan in the radix sort: linesearch 0.36 -> 0.23.  Launch list of two solves: `r2c/launches_c3.md`; per-kernel `ncu --set full` table of one Newton step: `r2c/c3_ncu_kernels.md`; stall sampling of the LDL' chain of the panel kernel: `r2b/panel_ldl_stalls.txt`.\n")
+o.append("Steps of the round's second half, factor / solve ms on C3, each with its A/B log: second-generation panel step 3.65 -> 2.72 (`r2b/panel_ab.log`); shared-memory fronts with per-row panel threads 2.72 -> 2.44; forked graph branches per level 2.44 / 1.32 -> 1.78 / 1.07 (`r2b/concurrency_ab.log`); cluster solves of the big fronts 1.07 -> 0.76 (`r2b/cluster_solve_ab.log`); cp.async staging in the small / mid solve kernels 0.77 -> 0.67; programmatic dependent launch along the panel chain 1.75 -> 1.66; per-digit scan in the radix sort: linesearch 0.36 -> 0.23.  Launch list of two solves: `r2g/launches_c3.md`; per-kernel `ncu --set full` table of one Newton step: `r2g/c3_ncu_kernels.md`; stall sampling of the LDL' chain of the panel kernel: `r2b/panel_ldl_stalls.txt`.\n")
 o.append("## C1 (n = 1000, m = 500) and C4 (Lasso path, n = 200k, m = 100k)\n")
 o.append("| | start of round 2 | HEAD | reference, same box |\n|---|---|---|---|")
 o.append("| C1 ms per cold solve (33 passes) | 32.1 | **%.1f** | %.1f |" % (c1["value"], c1["cpu_baseline"]["value"]))
