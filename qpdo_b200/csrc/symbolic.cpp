@@ -1,6 +1,7 @@
 // symbolic.cpp -- see symbolic.h.  Host-side, runs once per qpdo_setup.
 #include "symbolic.h"
 #include <thread>
+#include <functional>
 #include <atomic>
 #include <vector>
 #include <algorithm>
@@ -373,13 +374,23 @@ static qpdo_symbolic *analyze_full(int n, int m, const int *Qp, const int *Qi,
     qpdo_symbolic *S = (qpdo_symbolic *)calloc(1, sizeof(qpdo_symbolic));
     if (!S) return NULL;
     S->n = n; S->m = m; S->nsuper = ns; S->nlevel = nlevel;
-    S->perm = dup(perm); S->pinv = dup(pinv); S->sn_start = dup(sn_start); S->sn_nr = dup(sn_nr);
-    S->sn_rowptr = dup(rowptr); S->rows = dup(rows); S->rel = dup(rel); S->sn_parent = dup(sn_parent);
-    S->child_ptr = dup(child_ptr); S->child_idx = dup(child_idx); S->Lp = dup(Lp); S->Up = dup(Up);
-    S->sn_level = dup(level); S->level_ptr = dup(level_ptr); S->level_sn = dup(level_sn);
-    S->col2sn = dup(col2sn);
-    S->nnzK = nnzK; S->Kp = dup(Kp); S->Ki = dup(Ki); S->Kdst = dup(Kdst); S->Kq = dup(Kq);
-    S->Ktp = dup(Ktp); S->ntriple = ntriple; S->Kt_row = dup(Kt_row); S->Kt_a1 = dup(Kt_a1); S->Kt_a2 = dup(Kt_a2);
+    S->nnzK = nnzK; S->ntriple = ntriple;
+    {
+        // the copies are independent and mostly first-touch page faults of fresh allocations: the large ones (entry maps, product
+        // tables, row structure) each on a thread of their own when the problem is large, the rest here
+        const bool par = (size_t)nnzK + (size_t)ntriple > 400000 && std::thread::hardware_concurrency() >= 4;
+        std::vector<std::thread> th;
+        auto go = [&](std::function<void()> f) { if (par) th.emplace_back(f); else f(); };
+        go([&] { S->Kt_row = dup(Kt_row); }); go([&] { S->Kt_a1 = dup(Kt_a1); }); go([&] { S->Kt_a2 = dup(Kt_a2); });
+        go([&] { S->Kdst = dup(Kdst); S->Kq = dup(Kq); }); go([&] { S->Ktp = dup(Ktp); S->Ki = dup(Ki); });
+        go([&] { S->rows = dup(rows); S->rel = dup(rel); });
+        S->perm = dup(perm); S->pinv = dup(pinv); S->sn_start = dup(sn_start); S->sn_nr = dup(sn_nr);
+        S->sn_rowptr = dup(rowptr); S->sn_parent = dup(sn_parent);
+        S->child_ptr = dup(child_ptr); S->child_idx = dup(child_idx); S->Lp = dup(Lp); S->Up = dup(Up);
+        S->sn_level = dup(level); S->level_ptr = dup(level_ptr); S->level_sn = dup(level_sn);
+        S->col2sn = dup(col2sn); S->Kp = dup(Kp);
+        for (auto &x : th) x.join();
+    }
     S->lnz = 0; S->flops = 0;
     for (int j = 0; j < n; j++) { S->lnz += cc[j]; S->flops += (double)cc[j] * (double)cc[j]; }
     S->lnz_stored = Lp[ns]; S->usize = Up[ns]; S->max_front = max_front; S->max_nc = max_nc;
